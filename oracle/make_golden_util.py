@@ -1,0 +1,18 @@
+"""Pieces shared by make_golden.py (build container, imports the reference) and the tests
+(anywhere): the case list and the tensor fingerprint.  Test infrastructure only."""
+import numpy as np
+import torch
+
+CASES = [  # name, batch, H, W, steps, data seed
+    ("b2_32x32", 2, 32, 32, 2, 123),
+    ("b1_64x48", 1, 64, 48, 1, 7),
+    ("b3_32x40", 3, 32, 40, 1, 11),
+]
+
+
+def fingerprint(t: torch.Tensor) -> np.ndarray:
+    """[sum, abs-sum, sum of squares, first 13 values] -- small, order-sensitive enough."""
+    f = t.detach().double().flatten()
+    head = torch.zeros(13, dtype=torch.float64)
+    head[: min(13, f.numel())] = f[:13]
+    return torch.cat([torch.stack([f.sum(), f.abs().sum(), (f * f).sum()]), head]).numpy()
