@@ -1,0 +1,104 @@
+// Library-level entry points and the convolution dispatch (tcgen05 path vs fp32-accumulate SIMT path).
+#include <atomic>
+
+#include "common.cuh"
+
+namespace p2p {
+
+static thread_local std::string g_last_error;
+void set_error(const std::string& s) { g_last_error = s; }
+static std::atomic<long long> g_launches{0};
+void count_launches(int n) { g_launches += n; }
+
+// conv_simt.cu
+int conv_fwd_simt(const p2p_conv* c, const void* in, const void* w, const float* bias, void* out, int dtype,
+                  cudaStream_t st);
+int conv_dgrad_simt(const p2p_conv* c, const void* dout, const void* wt, void* din, int dtype, cudaStream_t st);
+int conv_wgrad_simt(const p2p_conv* c, const void* in, const void* dout, float* dw, int dtype, cudaStream_t st);
+// conv_tc.cu
+bool conv_fwd_tc_supported(const p2p_conv* c);
+bool conv_dgrad_tc_supported(const p2p_conv* c);
+bool conv_wgrad_tc_supported(const p2p_conv* c);
+int conv_fwd_tc(const p2p_conv* c, const void* in, const void* w, const float* bias, void* out, double* stats,
+                cudaStream_t st);
+int conv_dgrad_tc(const p2p_conv* c, const void* dout, const void* wt, void* din, cudaStream_t st);
+int conv_wgrad_tc(const p2p_conv* c, const void* in, const void* dout, float* dw, cudaStream_t st);
+
+static int check_conv(const p2p_conv* c) {
+  P2P_REQUIRE(c != nullptr, "null descriptor");
+  P2P_REQUIRE(c->N > 0 && c->Hi > 0 && c->Wi > 0 && c->Ho > 0 && c->Wo > 0, "empty tensor");
+  P2P_REQUIRE(c->Ci % 16 == 0 && c->Co % 16 == 0 && c->Ci > 0 && c->Co > 0, "stored channels must be multiples of 16");
+  P2P_REQUIRE(c->kh > 0 && c->kw > 0 && c->stride >= 1 && c->pad >= 0, "bad kernel geometry");
+  P2P_REQUIRE(c->co_real > 0 && c->co_real <= c->Co && c->ci_real > 0 && c->ci_real <= c->Ci, "bad real channel count");
+  P2P_REQUIRE((c->Ho - 1) * c->stride + c->kh - c->pad <= c->Hi + c->pad &&
+                  (c->Wo - 1) * c->stride + c->kw - c->pad <= c->Wi + c->pad,
+              "output larger than the padded input allows");
+  P2P_REQUIRE(c->act == P2P_ACT_NONE || c->act == P2P_ACT_LRELU, "epilogue activation must be none or leaky relu");
+  return 0;
+}
+
+static bool g_tc_checked = false, g_tc_ok = false;
+static bool device_tc() {
+  if (!g_tc_checked) {
+    int dev = 0, major = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess &&
+        cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) == cudaSuccess)
+      g_tc_ok = (major == 10);
+    g_tc_checked = true;
+  }
+  return g_tc_ok;
+}
+
+}  // namespace p2p
+
+using namespace p2p;
+
+extern "C" {
+
+int p2p_version(void) { return 100; }
+const char* p2p_last_error(void) { return g_last_error.c_str(); }
+int p2p_device_supports_tc(void) { return device_tc() ? 1 : 0; }
+long long p2p_launch_count(void) { return g_launches.load(); }
+
+int p2p_conv_fwd(const p2p_conv* c, const void* in, const void* w_packed, const float* bias, void* out, double* stats,
+                 int dtype, int impl, void* stream) {
+  if (int e = check_conv(c)) return e;
+  P2P_REQUIRE(in && w_packed && out, "null pointer");
+  P2P_REQUIRE(dtype == P2P_F32 || dtype == P2P_BF16, "unknown dtype");
+  cudaStream_t st = as_stream(stream);
+  const bool tc_ok = dtype == P2P_BF16 && device_tc() && conv_fwd_tc_supported(c);
+  P2P_REQUIRE(impl != P2P_IMPL_TC || tc_ok, "tcgen05 path does not support this shape / dtype / device");
+  if (impl != P2P_IMPL_SIMT && tc_ok) return conv_fwd_tc(c, in, w_packed, bias, out, stats, st);
+  if (int e = conv_fwd_simt(c, in, w_packed, bias, out, dtype, st)) return e;
+  if (stats != nullptr) {
+    P2P_REQUIRE(c->act == P2P_ACT_NONE, "statistics are taken before any activation");
+    return p2p_channel_stats(out, stats, (int64_t)c->N * c->Ho * c->Wo, c->Co, dtype, stream);
+  }
+  return 0;
+}
+
+int p2p_conv_dgrad(const p2p_conv* c, const void* dout, const void* wt_packed, void* din, int dtype, int impl,
+                   void* stream) {
+  if (int e = check_conv(c)) return e;
+  P2P_REQUIRE(dout && wt_packed && din, "null pointer");
+  P2P_REQUIRE(dtype == P2P_F32 || dtype == P2P_BF16, "unknown dtype");
+  cudaStream_t st = as_stream(stream);
+  const bool tc_ok = dtype == P2P_BF16 && device_tc() && conv_dgrad_tc_supported(c);
+  P2P_REQUIRE(impl != P2P_IMPL_TC || tc_ok, "tcgen05 path does not support this shape / dtype / device");
+  if (impl != P2P_IMPL_SIMT && tc_ok) return conv_dgrad_tc(c, dout, wt_packed, din, st);
+  return conv_dgrad_simt(c, dout, wt_packed, din, dtype, st);
+}
+
+int p2p_conv_wgrad(const p2p_conv* c, const void* in, const void* dout, float* dw_acc, int dtype, int impl,
+                   void* stream) {
+  if (int e = check_conv(c)) return e;
+  P2P_REQUIRE(in && dout && dw_acc, "null pointer");
+  P2P_REQUIRE(dtype == P2P_F32 || dtype == P2P_BF16, "unknown dtype");
+  cudaStream_t st = as_stream(stream);
+  const bool tc_ok = dtype == P2P_BF16 && device_tc() && conv_wgrad_tc_supported(c);
+  P2P_REQUIRE(impl != P2P_IMPL_TC || tc_ok, "tcgen05 path does not support this shape / dtype / device");
+  if (impl != P2P_IMPL_SIMT && tc_ok) return conv_wgrad_tc(c, in, dout, dw_acc, st);
+  return conv_wgrad_simt(c, in, dout, dw_acc, dtype, st);
+}
+
+}  // extern "C"

@@ -1,0 +1,711 @@
+// HBM-bound glue around the convolutions: layout changes at the API edge, reflection / upsample halos,
+// train-mode BatchNorm (statistics finalisation, apply, backward), activations and their gradients,
+// the discriminator's input pyramid.  All kernels move 8 channels (16-32 bytes) per thread, channel-fastest,
+// so every warp access is a run of full 32-byte sectors.
+#include "common.cuh"
+
+namespace p2p {
+
+// =================================================================================================
+// generator input: PixelUnshuffle(2) -> nearest x2 -> ReflectionPad(4)   (networks.py:173-187,457,399)
+// =================================================================================================
+template <typename T>
+__global__ void g_input_prep_kernel(const float* __restrict__ x, T* __restrict__ dst, int B, int H, int W) {
+  const int Hp = H + 8, Wp = W + 8;
+  const int64_t total = (int64_t)B * Hp * Wp * 2;  // two 8-channel groups
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int g = (int)(i & 1);
+    int64_t p = i >> 1;
+    const int px = (int)(p % Wp); p /= Wp;
+    const int py = (int)(p % Hp);
+    const int n = (int)(p / Hp);
+    const int uy = reflect_idx(py - 4, H), ux = reflect_idx(px - 4, W);   // position in the upsampled image
+    const int iy = uy >> 1, ix = ux >> 1;                                  // position in the unshuffled image
+    float v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int c = g * 8 + k;                                             // c = 4*c3 + 2*dy + dx
+      float val = 0.f;
+      if (c < 12) {
+        const int c3 = c >> 2, dy = (c >> 1) & 1, dx = c & 1;
+        val = x[(((int64_t)n * 3 + c3) * H + 2 * iy + dy) * W + 2 * ix + dx];
+      }
+      v[k] = val;
+    }
+    st8(dst + i * 8, v);
+  }
+}
+
+// =================================================================================================
+// per-channel statistics of a stored map (after SIMT convs; the tcgen05 epilogue produces them itself)
+// =================================================================================================
+template <typename T>
+__global__ void __launch_bounds__(256) channel_stats_kernel(const T* __restrict__ r, double* __restrict__ stats,
+                                                            int64_t pixels, int C) {
+  const int C8 = C >> 3;
+  const int c8 = threadIdx.x % C8, lane_p = threadIdx.x / C8, ppb = 256 / C8;
+  float s[8], q[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s[k] = q[k] = 0.f;
+  for (int64_t p = (int64_t)blockIdx.x * ppb + lane_p; p < pixels; p += (int64_t)gridDim.x * ppb) {
+    float v[8];
+    ld8(r + p * C + c8 * 8, v);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { s[k] += v[k]; q[k] += v[k] * v[k]; }
+  }
+  __shared__ float sh[2][8][256];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) { sh[0][k][threadIdx.x] = s[k]; sh[1][k][threadIdx.x] = q[k]; }
+  __syncthreads();
+  // thread t < 2*C sums one (which, channel) column over the ppb pixel lanes
+  for (int t = threadIdx.x; t < 2 * C; t += 256) {
+    const int which = t / C, c = t % C;
+    double a = 0.0;
+    for (int l = 0; l < ppb; ++l) a += (double)sh[which][c & 7][l * C8 + (c >> 3)];
+    atomicAdd(stats + which * C + c, a);
+  }
+}
+
+// =================================================================================================
+// BatchNorm bookkeeping
+// =================================================================================================
+__global__ void bn_finalize_kernel(const double* __restrict__ stats, int64_t count, const float* __restrict__ gamma,
+                                   const float* __restrict__ beta, float* running_mean, float* running_var,
+                                   int64_t* nbt, float* __restrict__ sb, int c_real, int C, int training) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c == 0 && training && nbt != nullptr) *nbt += 1;
+  if (c >= C) return;
+  float scale = 0.f, shift = 0.f, mean = 0.f, invstd = 0.f;
+  if (c < c_real) {
+    if (training) {
+      const double m = stats[c] / (double)count;
+      double var = stats[C + c] / (double)count - m * m;
+      var = var < 0.0 ? 0.0 : var;
+      mean = (float)m;
+      invstd = (float)(1.0 / sqrt(var + 1e-5));
+      if (running_mean != nullptr) {
+        const double unb = count > 1 ? var * (double)count / (double)(count - 1) : var;
+        running_mean[c] = 0.9f * running_mean[c] + 0.1f * mean;
+        running_var[c] = 0.9f * running_var[c] + 0.1f * (float)unb;
+      }
+    } else {
+      mean = running_mean[c];
+      invstd = rsqrtf(running_var[c] + 1e-5f);
+    }
+    scale = gamma[c] * invstd;
+    shift = beta[c] - mean * scale;
+  }
+  sb[c] = scale;
+  sb[C + c] = shift;
+  sb[2 * C + c] = mean;
+  sb[3 * C + c] = invstd;
+}
+
+__device__ __forceinline__ float act_fwd(float z, int act, float a) {
+  switch (act) {
+    case P2P_ACT_RELU: return z > 0.f ? z : 0.f;
+    case P2P_ACT_PRELU: return z > 0.f ? z : a * z;
+    case P2P_ACT_LRELU: return z > 0.f ? z : 0.2f * z;
+    case P2P_ACT_TANH: return tanhf(z);
+    default: return z;
+  }
+}
+__device__ __forceinline__ float act_bwd(float z, int act, float a) {
+  switch (act) {
+    case P2P_ACT_RELU: return z > 0.f ? 1.f : 0.f;
+    case P2P_ACT_PRELU: return z > 0.f ? 1.f : a;
+    case P2P_ACT_LRELU: return z > 0.f ? 1.f : 0.2f;
+    case P2P_ACT_TANH: { const float t = tanhf(z); return 1.f - t * t; }
+    default: return 1.f;
+  }
+}
+
+// y = act(scale*r + shift [+ skip]) -> padded / upsampled destination (gather form: one thread per
+// destination pixel x 8 channels, source found through the reflection and the >> log2(up)).
+template <typename T>
+__global__ void bn_act_store_kernel(const T* __restrict__ r, const float* __restrict__ sb, const T* __restrict__ skip,
+                                    int skip_pad, const float* __restrict__ prelu_a, T* __restrict__ dst, int B, int H,
+                                    int W, int C, int act, int up, int pad) {
+  const int C8 = C >> 3, Hu = H * up, Wu = W * up, Hd = Hu + 2 * pad, Wd = Wu + 2 * pad;
+  const int sh = up == 2 ? 1 : 0;
+  const float a = prelu_a != nullptr ? *prelu_a : 0.f;
+  const int64_t total = (int64_t)B * Hd * Wd * C8;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % C8);
+    int64_t p = i / C8;
+    const int dx = (int)(p % Wd); p /= Wd;
+    const int dy = (int)(p % Hd);
+    const int n = (int)(p / Hd);
+    const int sy = reflect_idx(dy - pad, Hu) >> sh, sx = reflect_idx(dx - pad, Wu) >> sh;
+    float v[8];
+    ld8(r + (((int64_t)n * H + sy) * W + sx) * C + c8 * 8, v);
+    float sk[8];
+    if (skip != nullptr)
+      ld8(skip + (((int64_t)n * (H + 2 * skip_pad) + sy + skip_pad) * (W + 2 * skip_pad) + sx + skip_pad) * C + c8 * 8, sk);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int c = c8 * 8 + k;
+      float z = sb != nullptr ? fmaf(v[k], sb[c], sb[C + c]) : v[k];
+      if (skip != nullptr) z += sk[k];
+      v[k] = act_fwd(z, act, a);
+    }
+    st8(dst + i * 8, v);
+  }
+}
+
+// generator output: y = act(scale*r + shift) -> NCHW fp32 [B,c_real,H,W]
+template <typename T>
+__global__ void bn_act_store_nchw_kernel(const T* __restrict__ r, const float* __restrict__ sb,
+                                         const float* __restrict__ prelu_a, float* __restrict__ out, int B, int H, int W,
+                                         int C, int c_real, int act) {
+  const float a = prelu_a != nullptr ? *prelu_a : 0.f;
+  const int64_t total = (int64_t)B * c_real * H * W;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t p = i;
+    const int x = (int)(p % W); p /= W;
+    const int y = (int)(p % H); p /= H;
+    const int c = (int)(p % c_real);
+    const int n = (int)(p / c_real);
+    const float v = ldf(r + (((int64_t)n * H + y) * W + x) * C + c);
+    const float z = sb != nullptr ? fmaf(v, sb[c], sb[C + c]) : v;
+    out[i] = act_fwd(z, act, a);
+  }
+}
+
+// rows of the padded buffer that mirror onto upsampled row u (besides u+pad itself)
+__device__ __forceinline__ int fold_candidates(int u, int n, int pad, int out[3]) {
+  int cnt = 0;
+  out[cnt++] = u + pad;
+  if (u >= 1 && u <= pad) out[cnt++] = pad - u;                                   // top / left halo
+  if (u <= n - 2 && u >= n - 1 - pad) out[cnt++] = 2 * (n - 1) - u + pad;         // bottom / right halo
+  return cnt;
+}
+
+// backward pass 1 (see header).  One thread per source pixel x 8 channels; block = 256 threads laid out
+// as (C/8 channel groups) x (256/(C/8) pixel lanes) so the per-channel partial sums reduce through smem.
+template <typename T>
+__global__ void __launch_bounds__(256)
+    bn_act_bwd_reduce_kernel(const T* __restrict__ dpad, const T* __restrict__ g1, const T* __restrict__ g2,
+                             const float* __restrict__ g_nchw, const T* __restrict__ r, const float* __restrict__ sb,
+                             const T* __restrict__ skip, int skip_pad, const float* __restrict__ prelu_a,
+                             T* __restrict__ dz, double* __restrict__ red, double* __restrict__ dprelu, int B, int H,
+                             int W, int C, int c_real, int act, int up, int pad) {
+  const int C8 = C >> 3;
+  const int c8 = threadIdx.x % C8, lane_p = threadIdx.x / C8, ppb = 256 / C8;
+  const int Hu = H * up, Wu = W * up, Hd = Hu + 2 * pad, Wd = Wu + 2 * pad;
+  const float a = prelu_a != nullptr ? *prelu_a : 0.f;
+  const int64_t pixels = (int64_t)B * H * W;
+  float s1[8], s2[8];
+  float sa = 0.f;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s1[k] = s2[k] = 0.f;
+  for (int64_t p = (int64_t)blockIdx.x * ppb + lane_p; p < pixels; p += (int64_t)gridDim.x * ppb) {
+    const int x = (int)(p % W);
+    const int y = (int)((p / W) % H);
+    const int n = (int)(p / ((int64_t)W * H));
+    float g[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) g[k] = 0.f;
+    if (dpad != nullptr) {
+      for (int uy = y * up; uy < y * up + up; ++uy) {
+        int rows[3];
+        const int nr = fold_candidates(uy, Hu, pad, rows);
+        for (int ux = x * up; ux < x * up + up; ++ux) {
+          int cols[3];
+          const int nc = fold_candidates(ux, Wu, pad, cols);
+          for (int a_ = 0; a_ < nr; ++a_)
+            for (int b_ = 0; b_ < nc; ++b_) {
+              float t[8];
+              ld8(dpad + (((int64_t)n * Hd + rows[a_]) * Wd + cols[b_]) * C + c8 * 8, t);
+#pragma unroll
+              for (int k = 0; k < 8; ++k) g[k] += t[k];
+            }
+        }
+      }
+    }
+    if (g1 != nullptr) {
+      float t[8];
+      ld8(g1 + p * C + c8 * 8, t);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] += t[k];
+    }
+    if (g2 != nullptr) {
+      float t[8];
+      ld8(g2 + p * C + c8 * 8, t);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] += t[k];
+    }
+    if (g_nchw != nullptr) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int c = c8 * 8 + k;
+        if (c < c_real) g[k] += g_nchw[(((int64_t)n * c_real + c) * H + y) * W + x];
+      }
+    }
+    float rv[8], sk[8];
+    ld8(r + p * C + c8 * 8, rv);
+    if (skip != nullptr)
+      ld8(skip + (((int64_t)n * (H + 2 * skip_pad) + y + skip_pad) * (W + 2 * skip_pad) + x + skip_pad) * C + c8 * 8, sk);
+    float o[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int c = c8 * 8 + k;
+      float z = sb != nullptr ? fmaf(rv[k], sb[c], sb[C + c]) : rv[k];
+      if (skip != nullptr) z += sk[k];
+      const float d = (c < c_real) ? g[k] * act_bwd(z, act, a) : 0.f;
+      if (act == P2P_ACT_PRELU && z < 0.f && c < c_real) sa += g[k] * z;
+      o[k] = d;
+      const float dq = round_as(d, dz);
+      s1[k] += dq;
+      if (sb != nullptr) s2[k] += dq * (rv[k] - sb[2 * C + c]) * sb[3 * C + c];
+    }
+    st8(dz + p * C + c8 * 8, o);
+  }
+  if (red != nullptr) {
+    __shared__ float sh[2][8][256];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { sh[0][k][threadIdx.x] = s1[k]; sh[1][k][threadIdx.x] = s2[k]; }
+    __syncthreads();
+    for (int t = threadIdx.x; t < 2 * C; t += 256) {
+      const int which = t / C, c = t % C;
+      double acc = 0.0;
+      for (int l = 0; l < ppb; ++l) acc += (double)sh[which][c & 7][l * C8 + (c >> 3)];
+      atomicAdd(red + which * C + c, acc);
+    }
+  }
+  if (dprelu != nullptr && act == P2P_ACT_PRELU) {
+    const float tot = block_sum<float>(sa);
+    if (threadIdx.x == 0) atomicAdd(dprelu, (double)tot);
+  }
+}
+
+// backward pass 2
+template <typename T>
+__global__ void __launch_bounds__(256)
+    bn_bwd_apply_kernel(const T* __restrict__ dz, const T* __restrict__ r, const float* __restrict__ sb,
+                        const double* __restrict__ red, T* __restrict__ dr, float* __restrict__ dbias, int64_t pixels,
+                        int C, int c_real) {
+  const int C8 = C >> 3;
+  const int c8 = threadIdx.x % C8, lane_p = threadIdx.x / C8, ppb = 256 / C8;
+  float m1[8], m2[8], sc[8], mean[8], istd[8], sd[8];
+  const double inv = 1.0 / (double)pixels;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int c = c8 * 8 + k;
+    m1[k] = (float)(red[c] * inv);
+    m2[k] = (float)(red[C + c] * inv);
+    sc[k] = sb[c];
+    mean[k] = sb[2 * C + c];
+    istd[k] = sb[3 * C + c];
+    sd[k] = 0.f;
+  }
+  for (int64_t p = (int64_t)blockIdx.x * ppb + lane_p; p < pixels; p += (int64_t)gridDim.x * ppb) {
+    float d[8], rv[8];
+    ld8(dz + p * C + c8 * 8, d);
+    ld8(r + p * C + c8 * 8, rv);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float xh = (rv[k] - mean[k]) * istd[k];
+      const float v = (c8 * 8 + k < c_real) ? sc[k] * (d[k] - m1[k] - xh * m2[k]) : 0.f;
+      d[k] = v;
+      sd[k] += v;
+    }
+    st8(dr + p * C + c8 * 8, d);
+  }
+  if (dbias != nullptr) {
+    __shared__ float sh[8][256];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) sh[k][threadIdx.x] = sd[k];
+    __syncthreads();
+    for (int c = threadIdx.x; c < c_real; c += 256) {
+      float acc = 0.f;
+      for (int l = 0; l < ppb; ++l) acc += sh[c & 7][l * C8 + (c >> 3)];
+      atomicAdd(dbias + c, acc);
+    }
+  }
+}
+
+__global__ void bn_param_grad_kernel(const double* __restrict__ red, float* dgamma, float* dbeta, int C, int c_real) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c < c_real) {
+    dbeta[c] += (float)red[c];
+    dgamma[c] += (float)red[C + c];
+  }
+}
+
+__global__ void prelu_grad_finish_kernel(const double* d, float* g) { *g += (float)(*d); }
+
+// =================================================================================================
+// discriminator input pyramid
+// =================================================================================================
+__global__ void d_input_prep_kernel(const float* __restrict__ a, int ca, const float* __restrict__ b, int cb,
+                                    float* __restrict__ dst, int B, int H, int W) {
+  const int64_t total = (int64_t)B * H * W;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t hw = (int64_t)H * W;
+    const int n = (int)(i / hw);
+    const int64_t rem = i - (int64_t)n * hw;
+    float v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      float t = 0.f;
+      if (k < ca) t = a[((int64_t)n * ca + k) * hw + rem];
+      else if (b != nullptr && k < ca + cb) t = b[((int64_t)n * cb + (k - ca)) * hw + rem];
+      v[k] = t;
+    }
+    st8(dst + i * 8, v);
+  }
+}
+
+// AvgPool2d(3, 2, 1, count_include_pad=False), NHWC fp32 with C == 8
+__global__ void avgpool_fwd_kernel(const float* __restrict__ in, float* __restrict__ out, int B, int H, int W, int Ho,
+                                   int Wo) {
+  const int64_t total = (int64_t)B * Ho * Wo;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int ox = (int)(i % Wo);
+    const int oy = (int)((i / Wo) % Ho);
+    const int n = (int)(i / ((int64_t)Wo * Ho));
+    float acc[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+    int cnt = 0;
+    for (int ky = 0; ky < 3; ++ky) {
+      const int y = oy * 2 - 1 + ky;
+      if (y < 0 || y >= H) continue;
+      for (int kx = 0; kx < 3; ++kx) {
+        const int x = ox * 2 - 1 + kx;
+        if (x < 0 || x >= W) continue;
+        float v[8];
+        ld8(in + (((int64_t)n * H + y) * W + x) * 8, v);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] += v[k];
+        ++cnt;
+      }
+    }
+    const float invc = 1.f / (float)cnt;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k] *= invc;
+    st8(out + i * 8, acc);
+  }
+}
+
+__device__ __forceinline__ int pool_count(int o, int n) {  // valid taps of output o along one axis
+  int c = 0;
+  for (int k = 0; k < 3; ++k) {
+    const int y = o * 2 - 1 + k;
+    c += (y >= 0 && y < n);
+  }
+  return c;
+}
+
+__global__ void avgpool_bwd_add_kernel(const float* __restrict__ dout, float* __restrict__ din, int B, int H, int W,
+                                       int Ho, int Wo) {
+  const int64_t total = (int64_t)B * H * W;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int x = (int)(i % W);
+    const int y = (int)((i / W) % H);
+    const int n = (int)(i / ((int64_t)W * H));
+    float acc[8];
+    ld8(din + i * 8, acc);
+    // outputs oy with oy*2-1 <= y <= oy*2+1
+    for (int oy = (y) / 2; oy <= (y + 1) / 2; ++oy) {
+      if (oy < 0 || oy >= Ho || y < oy * 2 - 1 || y > oy * 2 + 1) continue;
+      const int cy = pool_count(oy, H);
+      for (int ox = (x) / 2; ox <= (x + 1) / 2; ++ox) {
+        if (ox < 0 || ox >= Wo || x < ox * 2 - 1 || x > ox * 2 + 1) continue;
+        const float wgt = 1.f / (float)(cy * pool_count(ox, W));
+        float v[8];
+        ld8(dout + (((int64_t)n * Ho + oy) * Wo + ox) * 8, v);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] += v[k] * wgt;
+      }
+    }
+    st8(din + i * 8, acc);
+  }
+}
+
+template <typename T>
+__global__ void cast_pad_channels_kernel(const float* __restrict__ in, T* __restrict__ out, int64_t pixels, int Cs,
+                                         int Cd) {
+  const int D8 = Cd >> 3;
+  const int64_t total = pixels * D8;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % D8);
+    const int64_t p = i / D8;
+    float v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = 0.f;
+    if (c8 * 8 < Cs) ld8(in + p * Cs + c8 * 8, v);
+    st8(out + i * 8, v);
+  }
+}
+
+template <typename T>
+__global__ void uncast_add_kernel(const T* __restrict__ in, float* __restrict__ out, int64_t pixels, int Cs, int Cd) {
+  const int S8 = Cs >> 3;
+  const int64_t total = pixels * S8;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % S8);
+    const int64_t p = i / S8;
+    float v[8], o[8];
+    ld8(in + p * Cd + c8 * 8, v);
+    ld8(out + i * 8, o);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) o[k] += v[k];
+    st8(out + i * 8, o);
+  }
+}
+
+__global__ void d_input_grad_kernel(const float* __restrict__ dx, float* __restrict__ db, int ca, int cb, int B, int H,
+                                    int W) {
+  const int64_t hw = (int64_t)H * W, total = (int64_t)B * cb * hw;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t rem = i % hw;
+    const int c = (int)((i / hw) % cb);
+    const int n = (int)(i / (hw * cb));
+    db[i] = dx[((int64_t)n * hw + rem) * 8 + ca + c];
+  }
+}
+
+// dz = (ga + gb) * act'(out), plus per-channel sum for the conv bias gradient
+template <typename T>
+__global__ void __launch_bounds__(256)
+    act_bwd_kernel(const T* __restrict__ out, const T* __restrict__ ga, const T* __restrict__ gb, T* __restrict__ dz,
+                   float* __restrict__ dbias, int64_t pixels, int C, int c_real, int act) {
+  const int C8 = C >> 3;
+  const int c8 = threadIdx.x % C8, lane_p = threadIdx.x / C8, ppb = 256 / C8;
+  float sd[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) sd[k] = 0.f;
+  for (int64_t p = (int64_t)blockIdx.x * ppb + lane_p; p < pixels; p += (int64_t)gridDim.x * ppb) {
+    float g[8], t[8], o[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) g[k] = 0.f;
+    if (ga != nullptr) {
+      ld8(ga + p * C + c8 * 8, t);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] += t[k];
+    }
+    if (gb != nullptr) {
+      ld8(gb + p * C + c8 * 8, t);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] += t[k];
+    }
+    if (act == P2P_ACT_LRELU) {
+      ld8(out + p * C + c8 * 8, o);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] *= (o[k] > 0.f ? 1.f : 0.2f);
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      if (c8 * 8 + k >= c_real) g[k] = 0.f;
+      sd[k] += round_as(g[k], dz);
+    }
+    st8(dz + p * C + c8 * 8, g);
+  }
+  if (dbias != nullptr) {
+    __shared__ float sh[8][256];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) sh[k][threadIdx.x] = sd[k];
+    __syncthreads();
+    for (int c = threadIdx.x; c < c_real; c += 256) {
+      float acc = 0.f;
+      for (int l = 0; l < ppb; ++l) acc += sh[c & 7][l * C8 + (c >> 3)];
+      atomicAdd(dbias + c, acc);
+    }
+  }
+}
+
+template <typename T>
+__global__ void nhwc_to_nchw_kernel(const T* __restrict__ in, float* __restrict__ out, int B, int H, int W, int C,
+                                    int c_real) {
+  const int64_t hw = (int64_t)H * W, total = (int64_t)B * c_real * hw;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t rem = i % hw;
+    const int c = (int)((i / hw) % c_real);
+    const int n = (int)(i / (hw * c_real));
+    out[i] = ldf(in + ((int64_t)n * hw + rem) * C + c);
+  }
+}
+
+template <typename T>
+__global__ void nchw_to_nhwc_kernel(const float* __restrict__ in, T* __restrict__ out, int B, int H, int W, int C,
+                                    int c_real) {
+  const int C8 = C >> 3;
+  const int64_t hw = (int64_t)H * W, total = (int64_t)B * hw * C8;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % C8);
+    const int64_t p = i / C8;
+    const int n = (int)(p / hw);
+    const int64_t rem = p - (int64_t)n * hw;
+    float v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int c = c8 * 8 + k;
+      v[k] = c < c_real ? in[((int64_t)n * c_real + c) * hw + rem] : 0.f;
+    }
+    st8(out + i * 8, v);
+  }
+}
+
+static inline int ew_grid(int64_t total, int block = 256) {
+  int64_t g = (total + block - 1) / block;
+  const int64_t cap = (int64_t)kSMs * 16;
+  return (int)(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+}  // namespace p2p
+
+using namespace p2p;
+
+extern "C" {
+
+int p2p_g_input_prep(const float* x, void* dst, int B, int H, int W, int dtype, void* stream) {
+  P2P_REQUIRE(x && dst && B > 0 && H > 0 && W > 0, "null pointer or empty shape");
+  P2P_REQUIRE(H % 4 == 0 && W % 4 == 0 && H >= 8 && W >= 8, "H and W must be multiples of 4 and >= 8");
+  const int64_t total = (int64_t)B * (H + 8) * (W + 8) * 2;
+  P2P_DISPATCH(dtype, g_input_prep_kernel<T><<<ew_grid(total), 256, 0, as_stream(stream)>>>(x, (T*)dst, B, H, W););
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_channel_stats(const void* r, double* stats, int64_t pixels, int C, int dtype, void* stream) {
+  P2P_REQUIRE(r && stats && pixels > 0, "null pointer or empty map");
+  P2P_REQUIRE(C % 16 == 0 && C <= 512, "C must be a multiple of 16, <= 512");
+  const int ppb = 256 / (C / 8);
+  P2P_DISPATCH(dtype, channel_stats_kernel<T><<<ew_grid(pixels, ppb), 256, 0, as_stream(stream)>>>((const T*)r, stats,
+                                                                                                pixels, C););
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_bn_finalize(const double* stats, int64_t count, const float* gamma, const float* beta, float* running_mean,
+                    float* running_var, int64_t* num_batches_tracked, float* sb, int c_real, int C, int training,
+                    void* stream) {
+  P2P_REQUIRE(gamma && beta && sb, "null pointer");
+  P2P_REQUIRE(training ? (stats != nullptr && count > 0) : (running_mean && running_var), "missing statistics");
+  bn_finalize_kernel<<<cdiv(C, 128), 128, 0, as_stream(stream)>>>(stats, count, gamma, beta, running_mean, running_var,
+                                                                 num_batches_tracked, sb, c_real, C, training);
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_bn_act_store(const void* r, const float* sb, const void* skip, int skip_pad, const float* prelu_a, void* dst,
+                     float* out_nchw, int B, int H, int W, int C, int c_real, int act, int up, int pad, int dtype,
+                     void* stream) {
+  P2P_REQUIRE(r && (dst || out_nchw), "null pointer");
+  P2P_REQUIRE(C % 16 == 0 && (up == 1 || up == 2) && pad >= 0, "bad geometry");
+  P2P_REQUIRE(pad < H * up && pad < W * up, "reflection pad must be smaller than the image");
+  P2P_REQUIRE(act != P2P_ACT_PRELU || prelu_a, "PReLU needs its slope");
+  if (out_nchw != nullptr) {
+    P2P_REQUIRE(skip == nullptr && up == 1, "NCHW output takes no skip / upsample");
+    const int64_t total = (int64_t)B * c_real * H * W;
+    P2P_DISPATCH(dtype, bn_act_store_nchw_kernel<T><<<ew_grid(total), 256, 0, as_stream(stream)>>>(
+                            (const T*)r, sb, prelu_a, out_nchw, B, H, W, C, c_real, act););
+    P2P_LAUNCH_CHECK();
+  }
+  const int64_t total = (int64_t)B * (H * up + 2 * pad) * (W * up + 2 * pad) * (C / 8);
+  P2P_DISPATCH(dtype, bn_act_store_kernel<T><<<ew_grid(total), 256, 0, as_stream(stream)>>>(
+                          (const T*)r, sb, (const T*)skip, skip_pad, prelu_a, (T*)dst, B, H, W, C, act, up, pad););
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_bn_act_bwd_reduce(const void* dpad, const void* g1, const void* g2, const float* g_nchw, const void* r,
+                          const float* sb, const void* skip, int skip_pad, const float* prelu_a, void* dz, double* red,
+                          double* dprelu, int B, int H, int W, int C, int c_real, int act, int up, int pad, int dtype,
+                          void* stream) {
+  P2P_REQUIRE(r && dz, "null pointer");
+  P2P_REQUIRE(dpad || g1 || g2 || g_nchw, "no incoming gradient");
+  P2P_REQUIRE(C % 16 == 0 && C <= 512 && (up == 1 || up == 2), "bad geometry");
+  P2P_REQUIRE(act != P2P_ACT_PRELU || prelu_a, "PReLU needs its slope");
+  const int ppb = 256 / (C / 8);
+  const int64_t pixels = (int64_t)B * H * W;
+  P2P_DISPATCH(dtype, bn_act_bwd_reduce_kernel<T><<<ew_grid(pixels, ppb), 256, 0, as_stream(stream)>>>(
+                          (const T*)dpad, (const T*)g1, (const T*)g2, g_nchw, (const T*)r, sb, (const T*)skip, skip_pad,
+                          prelu_a, (T*)dz, red, dprelu, B, H, W, C, c_real, act, up, pad););
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_bn_bwd_apply(const void* dz, const void* r, const float* sb, const double* red, void* dr, float* dgamma,
+                     float* dbeta, float* dbias, int64_t pixels, int C, int c_real, int dtype, void* stream) {
+  P2P_REQUIRE(dz && r && sb && red && dr, "null pointer");
+  P2P_REQUIRE(C % 16 == 0 && C <= 512, "C must be a multiple of 16, <= 512");
+  const int ppb = 256 / (C / 8);
+  P2P_DISPATCH(dtype, bn_bwd_apply_kernel<T><<<ew_grid(pixels, ppb), 256, 0, as_stream(stream)>>>(
+                          (const T*)dz, (const T*)r, sb, red, (T*)dr, dbias, pixels, C, c_real););
+  if (dgamma != nullptr && dbeta != nullptr) {
+    bn_param_grad_kernel<<<cdiv(C, 128), 128, 0, as_stream(stream)>>>(red, dgamma, dbeta, C, c_real);
+    count_launches(1);
+  }
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_prelu_grad_finish(const double* dprelu, float* grad, void* stream) {
+  P2P_REQUIRE(dprelu && grad, "null pointer");
+  prelu_grad_finish_kernel<<<1, 1, 0, as_stream(stream)>>>(dprelu, grad);
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_d_input_prep(const float* a, int ca, const float* b, int cb, float* dst, int B, int H, int W, void* stream) {
+  P2P_REQUIRE(a && dst && ca > 0 && ca + (b ? cb : 0) <= 8, "at most 8 input channels");
+  d_input_prep_kernel<<<ew_grid((int64_t)B * H * W), 256, 0, as_stream(stream)>>>(a, ca, b, b ? cb : 0, dst, B, H, W);
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_avgpool3s2_fwd(const float* in, float* out, int B, int H, int W, int C, void* stream) {
+  P2P_REQUIRE(in && out && C == 8, "NHWC fp32 with 8 stored channels");
+  const int Ho = (H - 1) / 2 + 1, Wo = (W - 1) / 2 + 1;
+  avgpool_fwd_kernel<<<ew_grid((int64_t)B * Ho * Wo), 256, 0, as_stream(stream)>>>(in, out, B, H, W, Ho, Wo);
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_avgpool3s2_bwd_add(const float* dout, float* din, int B, int H, int W, int C, void* stream) {
+  P2P_REQUIRE(dout && din && C == 8, "NHWC fp32 with 8 stored channels");
+  const int Ho = (H - 1) / 2 + 1, Wo = (W - 1) / 2 + 1;
+  avgpool_bwd_add_kernel<<<ew_grid((int64_t)B * H * W), 256, 0, as_stream(stream)>>>(dout, din, B, H, W, Ho, Wo);
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_cast_pad_channels(const float* in, void* out, int64_t pixels, int Cs, int Cd, int dtype, void* stream) {
+  P2P_REQUIRE(in && out && Cs % 8 == 0 && Cd % 8 == 0 && Cd >= Cs, "channel counts must be multiples of 8");
+  P2P_DISPATCH(dtype, cast_pad_channels_kernel<T><<<ew_grid(pixels * (Cd / 8)), 256, 0, as_stream(stream)>>>(
+                          in, (T*)out, pixels, Cs, Cd););
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_uncast_add(const void* in, float* out, int64_t pixels, int Cs, int Cd, int dtype, void* stream) {
+  P2P_REQUIRE(in && out && Cs % 8 == 0 && Cd % 8 == 0 && Cd >= Cs, "channel counts must be multiples of 8");
+  P2P_DISPATCH(dtype, uncast_add_kernel<T><<<ew_grid(pixels * (Cs / 8)), 256, 0, as_stream(stream)>>>(
+                          (const T*)in, out, pixels, Cs, Cd););
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_d_input_grad(const float* dx, float* db, int ca, int cb, int B, int H, int W, void* stream) {
+  P2P_REQUIRE(dx && db && ca + cb <= 8, "at most 8 input channels");
+  d_input_grad_kernel<<<ew_grid((int64_t)B * cb * H * W), 256, 0, as_stream(stream)>>>(dx, db, ca, cb, B, H, W);
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_act_bwd(const void* out, const void* g_a, const void* g_b, void* dz, float* dbias, int64_t pixels, int C,
+                int c_real, int act, int dtype, void* stream) {
+  P2P_REQUIRE(dz && (g_a || g_b), "null pointer");
+  P2P_REQUIRE(act == P2P_ACT_NONE || (act == P2P_ACT_LRELU && out), "LeakyReLU gradient needs the forward output");
+  P2P_REQUIRE(C % 16 == 0 && C <= 512, "C must be a multiple of 16, <= 512");
+  const int ppb = 256 / (C / 8);
+  P2P_DISPATCH(dtype, act_bwd_kernel<T><<<ew_grid(pixels, ppb), 256, 0, as_stream(stream)>>>(
+                          (const T*)out, (const T*)g_a, (const T*)g_b, (T*)dz, dbias, pixels, C, c_real, act););
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_nhwc_to_nchw(const void* in, float* out, int B, int H, int W, int C, int c_real, int dtype, void* stream) {
+  P2P_REQUIRE(in && out && c_real <= C, "null pointer");
+  P2P_DISPATCH(dtype, nhwc_to_nchw_kernel<T><<<ew_grid((int64_t)B * c_real * H * W), 256, 0, as_stream(stream)>>>(
+                          (const T*)in, out, B, H, W, C, c_real););
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_nchw_to_nhwc(const float* in, void* out, int B, int H, int W, int C, int c_real, int dtype, void* stream) {
+  P2P_REQUIRE(in && out && c_real <= C && C % 8 == 0, "null pointer");
+  P2P_DISPATCH(dtype, nchw_to_nhwc_kernel<T><<<ew_grid((int64_t)B * H * W * (C / 8)), 256, 0, as_stream(stream)>>>(
+                          in, (T*)out, B, H, W, C, c_real););
+  P2P_LAUNCH_CHECK();
+}
+
+}  // extern "C"

@@ -1,0 +1,208 @@
+// Parameter-side kernels: weight packing for the two GEMM operand layouts, gradient unpacking into
+// PyTorch's [co][ci][kh][kw] parameter layout, and the hand-rolled SpectralNorm of the reference
+// (networks.py:525-582): one power iteration per forward, W = W_bar / sigma, sigma differentiable in W_bar.
+#include "common.cuh"
+
+namespace p2p {
+
+// w [co_real][ci_real][kh][kw] fp32 -> wp [Co][kh][kw][Ci], wt [Ci][kh][kw][Co]   (zeros in the padding)
+template <typename T>
+__global__ void pack_weights_kernel(const float* __restrict__ w, const float* __restrict__ sigma, T* __restrict__ wp,
+                                    T* __restrict__ wt, int co_real, int ci_real, int Co, int Ci, int kh, int kw) {
+  const float inv = sigma != nullptr ? 1.f / *sigma : 1.f;
+  const int taps = kh * kw;
+  const int64_t total = (int64_t)Co * taps * Ci;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    if (wp != nullptr) {  // i enumerates [Co][tap][Ci]
+      const int ci = (int)(i % Ci);
+      const int tap = (int)((i / Ci) % taps);
+      const int co = (int)(i / ((int64_t)Ci * taps));
+      const float v = (co < co_real && ci < ci_real) ? w[((int64_t)co * ci_real + ci) * taps + tap] * inv : 0.f;
+      stf(wp + i, v);
+    }
+    if (wt != nullptr) {  // i enumerates [Ci][tap][Co]
+      const int co = (int)(i % Co);
+      const int tap = (int)((i / Co) % taps);
+      const int ci = (int)(i / ((int64_t)Co * taps));
+      const float v = (co < co_real && ci < ci_real) ? w[((int64_t)co * ci_real + ci) * taps + tap] * inv : 0.f;
+      stf(wt + i, v);
+    }
+  }
+}
+
+// grad[co][ci][tap] += scale * acc[tap][ci][co];  optionally dot += sum acc * w
+__global__ void __launch_bounds__(256) unpack_wgrad_kernel(const float* __restrict__ acc, float* __restrict__ grad,
+                                                           const float* __restrict__ w, const float* __restrict__ sigma,
+                                                           float* __restrict__ dot, int co_real, int ci_real, int Co,
+                                                           int Ci, int taps) {
+  const float scale = sigma != nullptr ? 1.f / *sigma : 1.f;
+  const int64_t total = (int64_t)co_real * ci_real * taps;
+  float d = 0.f;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int tap = (int)(i % taps);
+    const int ci = (int)((i / taps) % ci_real);
+    const int co = (int)(i / ((int64_t)taps * ci_real));
+    const float a = acc[((int64_t)tap * Ci + ci) * Co + co];
+    grad[i] += a * scale;
+    if (dot != nullptr) d += a * w[i];
+  }
+  if (dot != nullptr) {
+    const float tot = block_sum<float>(d);
+    if (threadIdx.x == 0) atomicAdd(dot, tot);
+  }
+}
+
+// d/dW_bar of W = W_bar / sigma, sigma = u^T W_bar v:  gW_bar = gW/sigma - (sum gW*W_bar)/sigma^2 * u v^T.
+// `dot` holds sum(gW * W_bar) (gW = gradient w.r.t. the effective weight).
+__global__ void sn_weight_grad_kernel(float* __restrict__ grad, const float* __restrict__ dot,
+                                      const float* __restrict__ sigma, const float* __restrict__ u,
+                                      const float* __restrict__ v, int rows, int cols) {
+  const float s = *sigma;
+  const float coef = *dot / (s * s);
+  const int64_t total = (int64_t)rows * cols;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int k = (int)(i % cols);
+    const int r = (int)(i / cols);
+    grad[i] -= coef * u[r] * v[k];
+  }
+}
+
+// ---- batched power iteration ---------------------------------------------------------------------
+struct SnTable {
+  const float* w[P2P_SN_MAX_LAYERS];
+  float* u[P2P_SN_MAX_LAYERS];
+  float* v[P2P_SN_MAX_LAYERS];
+  float* sigma[P2P_SN_MAX_LAYERS];
+  int rows[P2P_SN_MAX_LAYERS];
+  int cols[P2P_SN_MAX_LAYERS];
+  int tmp_off[P2P_SN_MAX_LAYERS];  // offset of this layer's scratch (cols + rows floats)
+};
+
+// t[k] = sum_r W[r][k] u[r]      grid (ceil(cols/256), layers)
+__global__ void sn_wt_u_kernel(SnTable tb, float* __restrict__ tmp) {
+  const int l = blockIdx.y;
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  const int rows = tb.rows[l], cols = tb.cols[l];
+  if (k >= cols) return;
+  const float* w = tb.w[l];
+  const float* u = tb.u[l];
+  float acc = 0.f;
+  for (int r = 0; r < rows; ++r) acc = fmaf(w[(int64_t)r * cols + k], u[r], acc);
+  tmp[tb.tmp_off[l] + k] = acc;
+}
+
+// v = t / (|t| + eps)            grid (layers), block 1024
+__global__ void __launch_bounds__(1024) sn_norm_v_kernel(SnTable tb, const float* __restrict__ tmp) {
+  const int l = blockIdx.x;
+  const int cols = tb.cols[l];
+  const float* t = tmp + tb.tmp_off[l];
+  float ss = 0.f;
+  for (int k = threadIdx.x; k < cols; k += blockDim.x) ss += t[k] * t[k];
+  __shared__ float nrm;
+  const float tot = block_sum<float>(ss);
+  if (threadIdx.x == 0) nrm = sqrtf(tot) + 1e-12f;
+  __syncthreads();
+  float* v = tb.v[l];
+  for (int k = threadIdx.x; k < cols; k += blockDim.x) v[k] = t[k] / nrm;
+}
+
+// s[r] = sum_k W[r][k] v[k]      one warp per row; grid (ceil(rows/8), layers), block 256
+__global__ void __launch_bounds__(256) sn_w_v_kernel(SnTable tb, float* __restrict__ tmp) {
+  const int l = blockIdx.y;
+  const int rows = tb.rows[l], cols = tb.cols[l];
+  const int r = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (r >= rows) return;
+  const float* w = tb.w[l] + (int64_t)r * cols;
+  const float* v = tb.v[l];
+  float acc = 0.f;
+  for (int k = lane * 4; k < cols; k += 128) {
+    const float4 a = *reinterpret_cast<const float4*>(w + k);
+    const float4 b = *reinterpret_cast<const float4*>(v + k);
+    acc += a.x * b.x + a.y * b.y + a.z * b.z + a.w * b.w;
+  }
+  acc = warp_sum(acc);
+  if (lane == 0) tmp[tb.tmp_off[l] + cols + r] = acc;
+}
+
+// u = s / (|s| + eps); sigma = u . s        grid (layers), block 512
+__global__ void __launch_bounds__(512) sn_norm_u_kernel(SnTable tb, const float* __restrict__ tmp) {
+  const int l = blockIdx.x;
+  const int rows = tb.rows[l], cols = tb.cols[l];
+  const float* s = tmp + tb.tmp_off[l] + cols;
+  float ss = 0.f;
+  for (int r = threadIdx.x; r < rows; r += blockDim.x) ss += s[r] * s[r];
+  __shared__ float nrm, tot_s;
+  const float tot = block_sum<float>(ss);
+  if (threadIdx.x == 0) { tot_s = tot; nrm = sqrtf(tot) + 1e-12f; }
+  __syncthreads();
+  float* u = tb.u[l];
+  for (int r = threadIdx.x; r < rows; r += blockDim.x) u[r] = s[r] / nrm;
+  if (threadIdx.x == 0) *tb.sigma[l] = tot_s / nrm;
+}
+
+}  // namespace p2p
+
+using namespace p2p;
+
+extern "C" {
+
+int p2p_pack_weights(const float* w, const float* sigma, void* w_packed, void* wt_packed, int co_real, int ci_real,
+                     int Co, int Ci, int kh, int kw, int dtype, void* stream) {
+  P2P_REQUIRE(w && (w_packed || wt_packed), "null pointer");
+  P2P_REQUIRE(co_real <= Co && ci_real <= Ci && Co % 16 == 0 && Ci % 16 == 0, "stored channels must be multiples of 16");
+  const int64_t total = (int64_t)Co * kh * kw * Ci;
+  int64_t blocks = (total + 255) / 256;
+  if (blocks > kSMs * 16) blocks = kSMs * 16;
+  P2P_DISPATCH(dtype, pack_weights_kernel<T><<<(int)blocks, 256, 0, as_stream(stream)>>>(
+                          w, sigma, (T*)w_packed, (T*)wt_packed, co_real, ci_real, Co, Ci, kh, kw););
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_unpack_wgrad(const float* dw_acc, float* grad, const float* w, const float* sigma, float* dot, int co_real,
+                     int ci_real, int Co, int Ci, int kh, int kw, void* stream) {
+  P2P_REQUIRE(dw_acc && grad, "null pointer");
+  P2P_REQUIRE(dot == nullptr || w != nullptr, "dot needs the weights");
+  const int64_t total = (int64_t)co_real * ci_real * kh * kw;
+  int64_t blocks = (total + 255) / 256;
+  if (blocks > kSMs * 8) blocks = kSMs * 8;
+  unpack_wgrad_kernel<<<(int)blocks, 256, 0, as_stream(stream)>>>(dw_acc, grad, w, sigma, dot, co_real, ci_real, Co, Ci,
+                                                                 kh * kw);
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_sn_weight_grad(float* grad_wbar, const float* dot, const float* sigma, const float* u, const float* v, int rows,
+                       int cols, void* stream) {
+  P2P_REQUIRE(grad_wbar && dot && sigma && u && v, "null pointer");
+  const int64_t total = (int64_t)rows * cols;
+  int64_t blocks = (total + 255) / 256;
+  if (blocks > kSMs * 8) blocks = kSMs * 8;
+  sn_weight_grad_kernel<<<(int)blocks, 256, 0, as_stream(stream)>>>(grad_wbar, dot, sigma, u, v, rows, cols);
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_spectral_norm(int n_layers, const float* const* w_host, float* const* u_host, float* const* v_host,
+                      float* const* sigma_host, const int32_t* rows_host, const int32_t* cols_host, float* tmp,
+                      void* stream) {
+  P2P_REQUIRE(n_layers >= 1 && n_layers <= P2P_SN_MAX_LAYERS, "1..16 layers per call");
+  P2P_REQUIRE(w_host && u_host && v_host && sigma_host && rows_host && cols_host && tmp, "null pointer");
+  SnTable tb;
+  int off = 0, max_rows = 0, max_cols = 0;
+  for (int l = 0; l < n_layers; ++l) {
+    P2P_REQUIRE(w_host[l] && u_host[l] && v_host[l] && sigma_host[l], "null layer pointer");
+    P2P_REQUIRE(cols_host[l] % 4 == 0, "cols must be a multiple of 4");
+    tb.w[l] = w_host[l]; tb.u[l] = u_host[l]; tb.v[l] = v_host[l]; tb.sigma[l] = sigma_host[l];
+    tb.rows[l] = rows_host[l]; tb.cols[l] = cols_host[l]; tb.tmp_off[l] = off;
+    off += rows_host[l] + cols_host[l];
+    max_rows = rows_host[l] > max_rows ? rows_host[l] : max_rows;
+    max_cols = cols_host[l] > max_cols ? cols_host[l] : max_cols;
+  }
+  cudaStream_t st = as_stream(stream);
+  sn_wt_u_kernel<<<dim3(cdiv(max_cols, 256), n_layers), 256, 0, st>>>(tb, tmp);
+  sn_norm_v_kernel<<<n_layers, 1024, 0, st>>>(tb, tmp);
+  sn_w_v_kernel<<<dim3(cdiv(max_rows, 8), n_layers), 256, 0, st>>>(tb, tmp);
+  sn_norm_u_kernel<<<n_layers, 512, 0, st>>>(tb, tmp);
+  count_launches(3);
+  P2P_LAUNCH_CHECK();
+}
+
+}  // extern "C"

@@ -1,0 +1,464 @@
+"""Kernel schedules of the generator and discriminator: what `ExpandNetwork.forward` and
+`MultiscaleDiscriminator.forward` of the reference (networks.py:492-523, :734-755) and their
+autograd backward become when every tensor op is one of the C-ABI kernels.
+
+Each network is ONE torch.autograd.Function: forward enqueues the layer kernels and keeps the
+intermediate NHWC buffers on the ctx, backward enqueues dgrad / wgrad / BatchNorm-backward kernels in
+reverse order.  PyTorch is used for device memory, streams and the autograd edge only.
+
+Parameter gradients: when a parameter already has a `.grad` tensor (FusedAdam keeps them as views of
+one flat buffer) the kernels accumulate straight into it and autograd is handed None; otherwise a
+fresh gradient tensor is returned the usual way.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import _lib as L
+from ._lib import Conv, call, ptr
+
+_state = {"dtype": torch.bfloat16, "impl": L.IMPL_AUTO}
+
+
+def set_precision(mode: str) -> None:
+    """'bf16' (default): bf16 activations/weights, fp32 accumulation, tcgen05 convolutions.
+    'bf16-simt': same data types on the CUDA-core convolutions (debugging aid).
+    'fp32': the verification mode -- fp32 activations and CUDA-core fp32 convolutions."""
+    if mode == "bf16":
+        _state.update(dtype=torch.bfloat16, impl=L.IMPL_AUTO)
+    elif mode == "bf16-simt":
+        _state.update(dtype=torch.bfloat16, impl=L.IMPL_SIMT)
+    elif mode == "fp32":
+        _state.update(dtype=torch.float32, impl=L.IMPL_SIMT)
+    else:
+        raise ValueError("precision must be 'bf16', 'bf16-simt' or 'fp32'")
+
+
+def get_precision() -> str:
+    if _state["dtype"] == torch.float32:
+        return "fp32"
+    return "bf16" if _state["impl"] == L.IMPL_AUTO else "bf16-simt"
+
+
+def pad16(c: int) -> int:
+    return (c + 15) // 16 * 16
+
+
+def _empty(shape, dtype, dev):
+    return torch.empty(shape, dtype=dtype, device=dev)
+
+
+def _zeros(shape, dtype, dev):
+    return torch.zeros(shape, dtype=dtype, device=dev)
+
+
+def _grad_slot(p: torch.Tensor):
+    """(tensor the kernels accumulate into, value to hand back to autograd)"""
+    g = p.grad
+    if g is not None and g.dtype == torch.float32 and g.is_contiguous() and g.shape == p.shape:
+        return g, None
+    z = torch.zeros_like(p, dtype=torch.float32, memory_format=torch.contiguous_format)
+    return z, z
+
+
+class ConvPlan:
+    """Geometry + packed weights of one convolution layer for one forward pass."""
+
+    def __init__(self, N, Hi, Wi, Ci, cin_real, cout_real, k, stride, pad, act=L.ACT_NONE):
+        self.k, self.stride, self.pad = k, stride, pad
+        self.Ho = (Hi + 2 * pad - k) // stride + 1
+        self.Wo = (Wi + 2 * pad - k) // stride + 1
+        self.Co = pad16(cout_real)
+        self.desc = Conv(N, Hi, Wi, Ci, self.Ho, self.Wo, self.Co, k, k, stride, pad, cout_real, cin_real, act)
+        self.cin_real, self.cout_real, self.Ci, self.act = cin_real, cout_real, Ci, act
+        self.wp = self.wt = None
+
+    def pack(self, weight, sigma, dt, want_wt=True):
+        dev = weight.device
+        self.wp = _empty((self.Co, self.k, self.k, self.Ci), dt, dev)
+        self.wt = _empty((self.Ci, self.k, self.k, self.Co), dt, dev) if want_wt else None
+        call("p2p_pack_weights", ptr(weight), ptr(sigma), ptr(self.wp), ptr(self.wt), self.cout_real, self.cin_real,
+             self.Co, self.Ci, self.k, self.k, L.dtype_code(dt))
+
+    def fwd(self, x, bias, out, stats):
+        call("p2p_conv_fwd", C.byref(self.desc), ptr(x), ptr(self.wp), ptr(bias), ptr(out), ptr(stats),
+             L.dtype_code(x.dtype), _state["impl"])
+
+    def dgrad(self, dout, din):
+        call("p2p_conv_dgrad", C.byref(self.desc), ptr(dout), ptr(self.wt), ptr(din), L.dtype_code(dout.dtype),
+             _state["impl"])
+
+    def wgrad(self, x, dout, grad, sigma=None, dot=None, w_for_dot=None):
+        """grad ([co][ci][kh][kw] fp32) += d loss / d weight  (scaled by 1/sigma if given)"""
+        acc = _zeros((self.k, self.k, self.Ci, self.Co), torch.float32, x.device)
+        call("p2p_conv_wgrad", C.byref(self.desc), ptr(x), ptr(dout), ptr(acc), L.dtype_code(x.dtype), _state["impl"])
+        call("p2p_unpack_wgrad", ptr(acc), ptr(grad), ptr(w_for_dot), ptr(sigma), ptr(dot), self.cout_real,
+             self.cin_real, self.Co, self.Ci, self.k, self.k)
+
+
+# =====================================================================================================
+# Generator
+# =====================================================================================================
+# (conv attr, bn attr, cout, k, stride, activation, role);  role: 'plain' | 'res_a' | 'res_b'
+def _g_layers():
+    t = [("conv1", "in1_e", 32, 9, 1, L.ACT_PRELU, "plain"),
+         ("conv2", "in2_e", 64, 3, 2, L.ACT_PRELU, "plain"),
+         ("conv3", "in3_e", 128, 3, 2, L.ACT_PRELU, "plain")]
+    for r in range(1, 10):
+        t.append((f"res{r}.conv1", f"res{r}.in1", 128, 3, 1, L.ACT_RELU, "res_a"))
+        t.append((f"res{r}.conv2", f"res{r}.in2", 128, 3, 1, L.ACT_RELU, "res_b"))
+    t += [("deconv3", "in3_d", 64, 3, 1, L.ACT_PRELU, "plain"),
+          ("deconv2", "in2_d", 32, 3, 1, L.ACT_PRELU, "plain"),
+          ("deconv1", "in1_d", 3, 9, 1, L.ACT_TANH, "plain")]
+    return t
+
+
+G_LAYERS = _g_layers()
+G_N = len(G_LAYERS)  # 24 conv + BatchNorm stages
+
+
+class _Stage:
+    """One conv + BatchNorm + activation stage (or the long-skip add) and the buffers backward needs."""
+    __slots__ = ("li", "plan", "x_in", "r", "sb", "skip", "skip_pad", "skip_src", "r_src", "act", "up", "pad",
+                 "H", "W", "C", "c_real", "role")
+
+    def __init__(self):
+        self.skip = self.skip_src = self.r_src = self.plan = self.x_in = self.sb = None
+        self.skip_pad = 0
+        self.li = -1
+
+
+class GeneratorFunction(torch.autograd.Function):
+    """y = ExpandNetwork(x) (networks.py:492-523).
+    apply(x, prelu, aux, *params): `aux` = dict(buffers=[(running_mean, running_var, num_batches_tracked)] per
+    layer, training=bool, param_refs=[Parameter objects in the order of `params`, prelu first]);
+    params = per layer (conv.weight, conv.bias, bn.weight, bn.bias)."""
+
+    @staticmethod
+    def forward(ctx, x, prelu, aux, *params):
+        L.require_cuda(x, "generator input")
+        if x.dim() != 4 or x.shape[1] != 3:
+            raise L.P2PError("generator input must be [B,3,H,W]")
+        buffers, training = aux["buffers"], aux["training"]
+        B, _, H, W = x.shape
+        dt, dev = _state["dtype"], x.device
+        dc = L.dtype_code(dt)
+        x = x.detach().contiguous().float()
+        stages: List[_Stage] = []
+        cur = _empty((B, H + 8, W + 8, 16), dt, dev)
+        call("p2p_g_input_prep", ptr(x), ptr(cur), B, H, W, dc)
+        producer = None            # stage that wrote `cur`
+        cin_real = 12
+        block_in = block_in_src = long_skip = long_skip_src = None
+        out = None
+        for li, (name, _bn, cout, k, stride, act, role) in enumerate(G_LAYERS):
+            w, b, gamma, beta = params[4 * li: 4 * li + 4]
+            rm, rv, nbt = buffers[li]
+            plan = ConvPlan(B, cur.shape[1], cur.shape[2], cur.shape[3], cin_real, cout, k, stride, 0)
+            plan.pack(w, None, dt)
+            Ho, Wo, Co = plan.Ho, plan.Wo, plan.Co
+            r = _empty((B, Ho, Wo, Co), dt, dev)
+            stats = _zeros((2 * Co,), torch.float64, dev) if training else None
+            plan.fwd(cur, b, r, stats)
+            sb = _empty((4 * Co,), torch.float32, dev)
+            call("p2p_bn_finalize", ptr(stats), B * Ho * Wo, ptr(gamma), ptr(beta), ptr(rm), ptr(rv), ptr(nbt), ptr(sb),
+                 cout, Co, 1 if training else 0)
+            st = _Stage()
+            st.li, st.plan, st.x_in, st.r, st.sb, st.act, st.role = li, plan, cur, r, sb, act, role
+            st.H, st.W, st.C, st.c_real = Ho, Wo, Co, cout
+            if role == "res_a":
+                block_in, block_in_src = cur, producer
+            if role == "res_b":
+                st.skip, st.skip_pad, st.skip_src = block_in, 1, block_in_src
+            if li == G_N - 1:
+                st.up, st.pad = 1, 0
+                out = _empty((B, 3, H, W), torch.float32, dev)
+                call("p2p_bn_act_store", ptr(r), ptr(sb), None, 0, ptr(prelu), None, ptr(out), B, Ho, Wo, Co, cout, act,
+                     1, 0, dc)
+                stages.append(st)
+                break
+            if name == "res9.conv2":
+                # res9's output stays compact: its only consumer is the long-skip add, not a convolution
+                st.up, st.pad = 1, 0
+                y9 = _empty((B, Ho, Wo, Co), dt, dev)
+                call("p2p_bn_act_store", ptr(r), ptr(sb), ptr(st.skip), st.skip_pad, ptr(prelu), ptr(y9), None, B, Ho,
+                     Wo, Co, cout, act, 1, 0, dc)
+                stages.append(st)
+                # y = LeakyReLU(res + residual) (networks.py:514-515), then nearest x2 + reflect 1 for deconv3
+                ls = _Stage()
+                ls.r, ls.act, ls.role, ls.r_src = y9, L.ACT_LRELU, "long_skip", st
+                ls.H, ls.W, ls.C, ls.c_real = Ho, Wo, Co, cout
+                ls.skip, ls.skip_pad, ls.skip_src, ls.up, ls.pad = long_skip, 1, long_skip_src, 2, 1
+                cur = _empty((B, Ho * 2 + 2, Wo * 2 + 2, Co), dt, dev)
+                call("p2p_bn_act_store", ptr(y9), None, ptr(long_skip), 1, None, ptr(cur), None, B, Ho, Wo, Co, cout,
+                     L.ACT_LRELU, 2, 1, dc)
+                stages.append(ls)
+                producer = ls
+            else:
+                nxt_name, nxt_k = G_LAYERS[li + 1][0], G_LAYERS[li + 1][3]
+                st.up, st.pad = (2 if nxt_name in ("deconv3", "deconv2") else 1), nxt_k // 2
+                dst = _empty((B, Ho * st.up + 2 * st.pad, Wo * st.up + 2 * st.pad, Co), dt, dev)
+                call("p2p_bn_act_store", ptr(r), ptr(sb), ptr(st.skip), st.skip_pad, ptr(prelu), ptr(dst), None, B, Ho,
+                     Wo, Co, cout, act, st.up, st.pad, dc)
+                stages.append(st)
+                cur, producer = dst, st
+                if name == "conv3":
+                    long_skip, long_skip_src = cur, st
+            cin_real = cout
+        ctx.set_materialize_grads(False)
+        ctx.stages, ctx.prelu, ctx.param_refs = stages, prelu, aux["param_refs"]
+        ctx.geom, ctx.training = (B, H, W), training
+        return out
+
+    @staticmethod
+    def backward(ctx, g_out):
+        if ctx.needs_input_grad[0]:
+            raise L.P2PError("gradient w.r.t. the generator input is not implemented (the reference never uses it: "
+                             "its only consumer is the quantiser, whose gradient is zero)")
+        if not ctx.training:
+            raise L.P2PError("backward through the generator needs training-mode BatchNorm statistics")
+        if g_out is None:
+            return (None,) * (3 + 4 * G_N)
+        stages, prelu, refs = ctx.stages, ctx.prelu, ctx.param_refs
+        B, H, W = ctx.geom
+        dev, dt = g_out.device, stages[0].r.dtype
+        dc = L.dtype_code(dt)
+        g_out = g_out.contiguous().float()
+        dprelu = _zeros((1,), torch.float64, dev)
+        ret: List[Optional[torch.Tensor]] = [None] * (4 * G_N)
+        dpad = None            # gradient w.r.t. the (padded) buffer the stage being processed wrote
+        extra = {}             # id(stage) -> compact gradients addressed to that stage's output (skip paths)
+        for st in reversed(stages):
+            ex = extra.pop(id(st), [])
+            g1 = ex[0] if len(ex) > 0 else None
+            g2 = ex[1] if len(ex) > 1 else None
+            dz = _empty((B, st.H, st.W, st.C), dt, dev)
+            if st.role == "long_skip":
+                call("p2p_bn_act_bwd_reduce", ptr(dpad), None, None, None, ptr(st.r), None, ptr(st.skip), st.skip_pad,
+                     None, ptr(dz), None, None, B, st.H, st.W, st.C, st.c_real, st.act, st.up, st.pad, dc)
+                extra.setdefault(id(st.r_src), []).append(dz)      # res9 output
+                extra.setdefault(id(st.skip_src), []).append(dz)   # conv3 output (the long residual)
+                dpad = None
+                continue
+            li = st.li
+            pw, pb, pg, pbeta = refs[1 + 4 * li: 5 + 4 * li]
+            red = _zeros((2 * st.C,), torch.float64, dev)
+            call("p2p_bn_act_bwd_reduce", ptr(dpad), ptr(g1), ptr(g2), ptr(g_out) if li == G_N - 1 else None, ptr(st.r),
+                 ptr(st.sb), ptr(st.skip), st.skip_pad, ptr(prelu), ptr(dz), ptr(red), ptr(dprelu), B, st.H, st.W, st.C,
+                 st.c_real, st.act, st.up, st.pad, dc)
+            if st.role == "res_b":
+                extra.setdefault(id(st.skip_src), []).append(dz)   # z = bn + skip: the block input gets dz as is
+            dr = _empty((B, st.H, st.W, st.C), dt, dev)
+            gw, ret[4 * li] = _grad_slot(pw)
+            gb, ret[4 * li + 1] = _grad_slot(pb)
+            gg, ret[4 * li + 2] = _grad_slot(pg)
+            gbe, ret[4 * li + 3] = _grad_slot(pbeta)
+            call("p2p_bn_bwd_apply", ptr(dz), ptr(st.r), ptr(st.sb), ptr(red), ptr(dr), ptr(gg), ptr(gbe), ptr(gb),
+                 B * st.H * st.W, st.C, st.c_real, dc)
+            st.plan.wgrad(st.x_in, dr, gw)
+            if li > 0:
+                dpad = _empty(tuple(st.x_in.shape), dt, dev)
+                st.plan.dgrad(dr, dpad)
+            else:
+                dpad = None
+        gp, ret_p = _grad_slot(refs[0])
+        call("p2p_prelu_grad_finish", ptr(dprelu), ptr(gp))
+        ctx.stages = None
+        return (None, ret_p, None, *ret)
+
+
+# =====================================================================================================
+# Discriminator
+# =====================================================================================================
+def d_layers(input_nc=6, ndf=64):
+    """(cin, cout, stride, spectral_norm) of one scale, networks.py:764-784"""
+    return [(input_nc, ndf, 2, False), (ndf, ndf * 2, 2, True), (ndf * 2, ndf * 4, 2, True),
+            (ndf * 4, min(ndf * 8, 512), 1, True), (min(ndf * 8, 512), 1, 1, False)]
+
+
+NUM_D = 3
+
+
+def spectral_power_iteration(wbars: Sequence[torch.Tensor], us, vs) -> torch.Tensor:
+    """one batched power iteration (networks.py:537-547); returns sigma[n]; u, v are updated in place"""
+    n = len(wbars)
+    dev = wbars[0].device
+    sigma = _empty((n,), torch.float32, dev)
+    rows = [w.shape[0] for w in wbars]
+    cols = [w[0].numel() for w in wbars]
+    tmp = _empty((sum(rows) + sum(cols),), torch.float32, dev)
+    PA, IA = C.c_void_p * n, C.c_int32 * n
+    call("p2p_spectral_norm", n, PA(*[w.data_ptr() for w in wbars]), PA(*[u.data_ptr() for u in us]),
+         PA(*[v.data_ptr() for v in vs]), PA(*[sigma.data_ptr() + 4 * i for i in range(n)]), IA(*rows), IA(*cols),
+         ptr(tmp))
+    return sigma
+
+
+class DiscriminatorFunction(torch.autograd.Function):
+    """All three scales of MultiscaleDiscriminator (networks.py:734-755) in one Function.
+
+    apply(a, b, aux, *params):
+      a [B,ca,H,W], b [B,cb,H,W] or None -- the pair is concatenated on the fly (train.py:308,315,336);
+      aux = dict(layer_cfg=d_layers(..), sn_bufs=[(u, v)] for the spectral-norm layers in module order,
+                 param_refs=[Parameter objects in the order of `params`]);
+      params = per scale/layer (weight or weight_bar, bias) in module order scale0_layer0 .. scale2_layer4.
+    returns 15 stored maps [B,Ho,Wo,pad16(C)] in the working dtype, in the reference's result order:
+    full-resolution scale first (it runs the scale2_* modules, networks.py:749)."""
+
+    @staticmethod
+    def forward(ctx, a, b, aux, *params):
+        L.require_cuda(a, "discriminator input")
+        layer_cfg, sn_bufs = aux["layer_cfg"], aux["sn_bufs"]
+        dt, dev = _state["dtype"], a.device
+        dc = L.dtype_code(dt)
+        a = a.detach().contiguous().float()
+        ca, cb = a.shape[1], 0
+        if b is not None:
+            b = b.detach().contiguous().float()
+            cb = b.shape[1]
+        if ca + cb > 8:
+            raise L.P2PError("the discriminator input may have at most 8 channels")
+        B, _, H, W = a.shape
+        nl = len(layer_cfg)
+        sn_idx = [(sc, j) for sc in range(NUM_D) for j in range(nl) if layer_cfg[j][3]]
+        sig_of = {}
+        if sn_idx:
+            wbars = [params[2 * (sc * nl + j)].detach() for sc, j in sn_idx]
+            sigma_all = spectral_power_iteration(wbars, [u for u, _ in sn_bufs], [v for _, v in sn_bufs])
+            sig_of = {key: sigma_all[i:i + 1] for i, key in enumerate(sn_idx)}
+        # input pyramid in fp32 (8 stored channels), then cast to the working dtype (16 stored channels)
+        xs32 = [_empty((B, H, W, 8), torch.float32, dev)]
+        call("p2p_d_input_prep", ptr(a), ca, ptr(b), cb, ptr(xs32[0]), B, H, W)
+        for _i in range(NUM_D - 1):
+            h, w = xs32[-1].shape[1:3]
+            nx = _empty((B, (h - 1) // 2 + 1, (w - 1) // 2 + 1, 8), torch.float32, dev)
+            call("p2p_avgpool3s2_fwd", ptr(xs32[-1]), ptr(nx), B, h, w, 8)
+            xs32.append(nx)
+        outs, plans, inputs = [], [], []
+        for i in range(NUM_D):
+            sc = NUM_D - 1 - i
+            h, w = xs32[i].shape[1:3]
+            cur = _empty((B, h, w, 16), dt, dev)
+            call("p2p_cast_pad_channels", ptr(xs32[i]), ptr(cur), B * h * w, 8, 16, dc)
+            cin_real = ca + cb
+            for j, (_cin, cout, stride, _sn) in enumerate(layer_cfg):
+                wgt, bias = params[2 * (sc * nl + j)], params[2 * (sc * nl + j) + 1]
+                act = L.ACT_LRELU if j != nl - 1 else L.ACT_NONE
+                plan = ConvPlan(B, cur.shape[1], cur.shape[2], cur.shape[3], cin_real, cout, 4, stride, 2, act)
+                plan.pack(wgt, sig_of.get((sc, j)), dt)
+                o = _empty((B, plan.Ho, plan.Wo, plan.Co), dt, dev)
+                plan.fwd(cur, bias, o, None)
+                plans.append(plan)
+                inputs.append(cur)
+                outs.append(o)
+                cur, cin_real = o, cout
+        ctx.set_materialize_grads(False)
+        ctx.plans, ctx.inputs, ctx.outs_ref = plans, inputs, outs
+        ctx.sig_of, ctx.sn_bufs, ctx.sn_idx = sig_of, sn_bufs, sn_idx
+        ctx.layer_cfg, ctx.param_refs = layer_cfg, aux["param_refs"]
+        ctx.geom = (B, H, W, ca, cb)
+        ctx.pyr_shapes = [tuple(t.shape) for t in xs32]
+        return tuple(outs)
+
+    @staticmethod
+    def backward(ctx, *gouts):
+        plans, inputs, outs = ctx.plans, ctx.inputs, ctx.outs_ref
+        layer_cfg, refs = ctx.layer_cfg, ctx.param_refs
+        B, H, W, ca, cb = ctx.geom
+        nl = len(layer_cfg)
+        dev, dt = outs[0].device, outs[0].dtype
+        dc = L.dtype_code(dt)
+        need_a = ctx.needs_input_grad[0]
+        need_b = ctx.needs_input_grad[1] or need_a
+        need_w = [ctx.needs_input_grad[3 + 2 * k] for k in range(NUM_D * nl)]
+        need_bias = [ctx.needs_input_grad[4 + 2 * k] for k in range(NUM_D * nl)]
+        ret: List[Optional[torch.Tensor]] = [None] * (2 * NUM_D * nl)
+        sn_pos = {key: i for i, key in enumerate(ctx.sn_idx)}
+        dx32 = [None] * NUM_D       # fp32 gradient of each pyramid level (only when need_b)
+        for i in reversed(range(NUM_D)):
+            sc = NUM_D - 1 - i
+            g_next = None           # gradient arriving from the layer above (its dgrad output)
+            for j in reversed(range(nl)):
+                idx = i * nl + j
+                plan, x_in, o = plans[idx], inputs[idx], outs[idx]
+                gu = gouts[idx]
+                if gu is not None:
+                    if gu.dtype != dt or tuple(gu.shape) != tuple(o.shape):
+                        raise L.P2PError("gradient of a discriminator map must have the map's stored layout")
+                    gu = gu.contiguous()
+                if gu is None and g_next is None:
+                    continue        # nothing has reached this layer yet
+                k = sc * nl + j
+                cout = layer_cfg[j][1]
+                dz = _empty(tuple(o.shape), dt, dev)
+                gbias = None
+                if need_bias[k]:
+                    gbias, ret[2 * k + 1] = _grad_slot(refs[2 * k + 1])
+                call("p2p_act_bwd", ptr(o), ptr(gu), ptr(g_next), ptr(dz), ptr(gbias), B * plan.Ho * plan.Wo, plan.Co,
+                     cout, plan.act, dc)
+                if need_w[k]:
+                    pw = refs[2 * k]
+                    gw, ret[2 * k] = _grad_slot(pw)
+                    if layer_cfg[j][3]:
+                        sigma = ctx.sig_of[(sc, j)]
+                        dot = _zeros((1,), torch.float32, dev)
+                        # gW_bar = gW / sigma - (sum gW * W_bar) / sigma^2 * u v^T   (W = W_bar / sigma)
+                        plan.wgrad(x_in, dz, gw, sigma=sigma, dot=dot, w_for_dot=pw.detach())
+                        u, v = ctx.sn_bufs[sn_pos[(sc, j)]]      # read NOW, not at forward: quirk Q1
+                        call("p2p_sn_weight_grad", ptr(gw), ptr(dot), ptr(sigma), ptr(u), ptr(v), pw.shape[0],
+                             pw[0].numel())
+                    else:
+                        plan.wgrad(x_in, dz, gw)
+                if j > 0 or need_b:
+                    g_next = _empty(tuple(x_in.shape), dt, dev)
+                    plan.dgrad(dz, g_next)
+                else:
+                    g_next = None
+            if need_b and g_next is not None:
+                h, w = ctx.pyr_shapes[i][1:3]
+                d32 = _zeros((B, h, w, 8), torch.float32, dev)
+                call("p2p_uncast_add", ptr(g_next), ptr(d32), B * h * w, 8, 16, dc)
+                dx32[i] = d32
+        ga = gb = None
+        if need_b:
+            # fold the pyramid: d level i += avgpool_backward(d level i+1)
+            for i in reversed(range(NUM_D - 1)):
+                if dx32[i + 1] is None:
+                    continue
+                h, w = ctx.pyr_shapes[i][1:3]
+                if dx32[i] is None:
+                    dx32[i] = _zeros((B, h, w, 8), torch.float32, dev)
+                call("p2p_avgpool3s2_bwd_add", ptr(dx32[i + 1]), ptr(dx32[i]), B, h, w, 8)
+            if ctx.needs_input_grad[1]:
+                gb = _zeros((B, cb, H, W), torch.float32, dev)
+                if dx32[0] is not None:
+                    call("p2p_d_input_grad", ptr(dx32[0]), ptr(gb), ca, cb, B, H, W)
+            if need_a:
+                ga = _zeros((B, ca, H, W), torch.float32, dev)
+                if dx32[0] is not None:
+                    call("p2p_d_input_grad", ptr(dx32[0]), ptr(ga), 0, ca, B, H, W)
+        ctx.plans = ctx.inputs = ctx.outs_ref = None
+        return (ga, gb, None, *ret)
+
+
+class StoredToNCHW(torch.autograd.Function):
+    """stored map [B,H,W,pad16(C)] (working dtype) -> NCHW fp32 [B,C,H,W]: the drop-in API edge."""
+
+    @staticmethod
+    def forward(ctx, t, c_real):
+        B, H, W, Cs = t.shape
+        out = _empty((B, c_real, H, W), torch.float32, t.device)
+        call("p2p_nhwc_to_nchw", ptr(t), ptr(out), B, H, W, Cs, c_real, L.dtype_code(t.dtype))
+        ctx.meta = (B, H, W, Cs, c_real, t.dtype)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        B, H, W, Cs, c_real, dt = ctx.meta
+        g = g.contiguous().float()
+        out = _empty((B, H, W, Cs), dt, g.device)
+        call("p2p_nchw_to_nhwc", ptr(g), ptr(out), B, H, W, Cs, c_real, L.dtype_code(dt))
+        return out, None

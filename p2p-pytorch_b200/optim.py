@@ -1,0 +1,91 @@
+"""FusedAdam: torch.optim.Adam as the reference configures it (train.py:241-242 -- lr 2e-4, betas (0.5, 0.999),
+eps 1e-8, no weight decay, no amsgrad) as ONE kernel launch per network.
+
+Parameters are re-homed into one flat fp32 buffer (each `p.data` becomes a view of it), gradients live in a
+second flat buffer (each `p.grad` is a view, kept across steps: `zero_grad()` zeroes in place), and the
+moments in two more.  The backward kernels accumulate straight into the gradient views, the data-parallel
+all-reduce runs on slices of the flat gradient buffer, and `step()` is p2p_adam_step over the whole buffer:
+28 bytes of HBM traffic per parameter.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib as L
+from ._lib import call, ptr
+
+
+class FusedAdam(torch.optim.Optimizer):
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8):
+        params = [p for p in params]
+        if any(isinstance(p, dict) for p in params):
+            raise ValueError("FusedAdam takes a flat list of parameters (one group)")
+        super().__init__(params, dict(lr=lr, betas=betas, eps=eps))
+        self._ps = [p for p in self.param_groups[0]["params"] if p.requires_grad]
+        if not self._ps:
+            raise ValueError("no trainable parameters")
+        dev = self._ps[0].device
+        for p in self._ps:
+            L.require_cuda(p, "parameter")
+            if p.dtype != torch.float32 or p.device != dev:
+                raise ValueError("FusedAdam needs fp32 parameters on one device")
+        n = sum(p.numel() for p in self._ps)
+        self.numel = n
+        self.flat_p = torch.empty(n, dtype=torch.float32, device=dev)
+        self.flat_g = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.exp_avg = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=dev)
+        self._offsets = []
+        off = 0
+        with torch.no_grad():
+            for p in self._ps:
+                k = p.numel()
+                view = self.flat_p[off:off + k].view(p.shape)
+                view.copy_(p.data)
+                p.data = view
+                p.grad = self.flat_g[off:off + k].view(p.shape)
+                self._offsets.append(off)
+                off += k
+        self.steps = 0
+        self.grad_scale = 1.0   # set to 1/world_size by the data-parallel trainer (all-reduce is a sum)
+
+    def _rebind_grads(self):
+        """Make sure every p.grad is still the flat view (a caller may have used set_to_none or assigned one)."""
+        for p, off in zip(self._ps, self._offsets):
+            view_ptr = self.flat_g.data_ptr() + 4 * off
+            g = p.grad
+            if g is not None and g.data_ptr() == view_ptr:
+                continue
+            view = self.flat_g[off:off + p.numel()].view(p.shape)
+            if g is None:
+                view.zero_()
+            else:
+                view.copy_(g)
+            p.grad = view
+
+    def zero_grad(self, set_to_none: bool = False):
+        # gradients are persistent views of one buffer: zero it in place (one memset) and keep the views
+        self._rebind_grads()
+        self.flat_g.zero_()
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        if closure is not None:
+            raise NotImplementedError("closures are not supported")
+        self._rebind_grads()
+        g = self.param_groups[0]
+        self.steps += 1
+        call("p2p_adam_step", ptr(self.flat_p), ptr(self.flat_g), ptr(self.exp_avg), ptr(self.exp_avg_sq), self.numel,
+             float(g["lr"]), float(g["betas"][0]), float(g["betas"][1]), float(g["eps"]), self.steps,
+             float(self.grad_scale))
+
+    def state_dict(self):
+        return {"steps": self.steps, "exp_avg": self.exp_avg.clone(), "exp_avg_sq": self.exp_avg_sq.clone(),
+                "param_groups": [{k: v for k, v in self.param_groups[0].items() if k != "params"}]}
+
+    def load_state_dict(self, sd):
+        self.steps = int(sd["steps"])
+        self.exp_avg.copy_(sd["exp_avg"])
+        self.exp_avg_sq.copy_(sd["exp_avg_sq"])
+        for k, v in sd["param_groups"][0].items():
+            self.param_groups[0][k] = v

@@ -1,0 +1,106 @@
+"""The training iteration of the reference (train.py:294-390, VGG term off) on the fused kernels, with
+optional batch data parallelism (one process per GPU, NCCL all-reduce of the flat gradient buffers).
+
+Differences from running the reference loop verbatim on the drop-in modules (all result-preserving):
+  * the three discriminator passes take (real_a, image) pairs -- no torch.cat copy (train.py:308,315,336);
+  * the third pass treats D's weights as constants: the reference computes those weight gradients during
+    `loss_g.backward()` and throws them away at `optimizer_d.zero_grad()` (train.py:385-388);
+  * losses are the fused LSGAN / feature-matching / TV kernels on the stored maps;
+  * no `.item()` host syncs: `step()` returns device scalars.
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional
+
+import torch
+
+from . import engine as E
+from .losses import feature_matching_loss, lsgan_loss, tv_loss
+from .optim import FusedAdam
+
+
+class GradReducer:
+    """Sum-all-reduce of a flat gradient buffer in buckets on the NCCL stream; the mean is folded into Adam
+    (grad_scale = 1/world).  Buckets are slices of the flat buffer, launched asynchronously so that the other
+    network's backward overlaps the transfer."""
+
+    def __init__(self, group=None, bucket_bytes: int = 8 << 20):
+        import torch.distributed as dist
+        self.dist, self.group = dist, group
+        self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+        self.bucket = max(1, bucket_bytes // 4)
+        self.pending = []
+
+    def launch(self, flat: torch.Tensor):
+        if self.world == 1:
+            return
+        n = flat.numel()
+        # last layers' gradients are complete first and sit at the end of the flat buffer: send back to front
+        end = n
+        while end > 0:
+            beg = max(0, end - self.bucket)
+            self.pending.append(self.dist.all_reduce(flat[beg:end], op=self.dist.ReduceOp.SUM, group=self.group,
+                                                     async_op=True))
+            end = beg
+
+    def wait(self):
+        for h in self.pending:
+            h.wait()
+        self.pending = []
+
+
+class Pix2PixTrainer:
+    """optimizer_g / optimizer_d loop of train.py:241-242, :294-390."""
+
+    def __init__(self, net_g, net_d, lr: float = 2e-4, beta1: float = 0.5, process_group=None,
+                 bucket_bytes: int = 8 << 20):
+        self.net_g, self.net_d = net_g, net_d
+        self.optimizer_g = FusedAdam(net_g.parameters(), lr=lr, betas=(beta1, 0.999))
+        self.optimizer_d = FusedAdam([p for p in net_d.parameters() if p.requires_grad], lr=lr, betas=(beta1, 0.999))
+        self.red_g = GradReducer(process_group, bucket_bytes)
+        self.red_d = GradReducer(process_group, bucket_bytes)
+        self.world = self.red_g.world
+        self.optimizer_g.grad_scale = self.optimizer_d.grad_scale = 1.0 / self.world
+        self._c_reals = [c[1] for c in net_d._cfg]
+
+    def broadcast_parameters(self, src: int = 0):
+        """identical replicas at start (rank `src` wins), including BatchNorm buffers and SN u/v"""
+        if self.world == 1:
+            return
+        import torch.distributed as dist
+        dist.broadcast(self.optimizer_g.flat_p, src)
+        dist.broadcast(self.optimizer_d.flat_p, src)
+        for net in (self.net_g, self.net_d):
+            for b in net.buffers():
+                dist.broadcast(b, src)
+            for p in net.parameters():
+                if not p.requires_grad:
+                    dist.broadcast(p.data, src)
+
+    def step(self, real_a: torch.Tensor, real_b: torch.Tensor, g_input: torch.Tensor) -> Dict[str, torch.Tensor]:
+        net_g, net_d, cr = self.net_g, self.net_d, self._c_reals
+        last = lambda maps: [s[-1] for s in maps]                                         # noqa: E731
+        ones = [1] * 3
+        fake_b = net_g(g_input)                                                           # train.py:300
+        pred_fake_d = net_d.forward_stored(real_a, fake_b.detach())                       # :308-309
+        loss_d_fake = lsgan_loss(last(pred_fake_d), ones, 0.0)                            # :310
+        pred_real = net_d.forward_stored(real_a, real_b)                                  # :315-316
+        loss_d_real = lsgan_loss(last(pred_real), ones, 1.0)                              # :317
+        loss_d = (loss_d_fake + loss_d_real) * 0.5                                        # :320
+        pred_fake = net_d.forward_stored(real_a, fake_b, frozen=True)                     # :336-337
+        loss_g_gan = lsgan_loss(last(pred_fake), ones, 1.0)                               # :338
+        loss_feat = feature_matching_loss(pred_fake, pred_real, cr)                       # :344-351
+        loss_tv = tv_loss(fake_b)                                                         # :378
+        loss_g = loss_g_gan + loss_feat + loss_tv                                         # :353,:380
+        self.optimizer_g.zero_grad()                                                      # :384
+        self.optimizer_d.zero_grad()                                                      # :388 (hoisted: D grads untouched above)
+        loss_g.backward()                                                                 # :385
+        self.red_g.launch(self.optimizer_g.flat_g)        # overlaps with D's backward below
+        loss_d.backward()                                                                 # :389
+        self.red_d.launch(self.optimizer_d.flat_g)
+        self.red_g.wait()
+        self.optimizer_g.step()                                                           # :386
+        self.red_d.wait()
+        self.optimizer_d.step()                                                           # :390
+        return {"fake_b": fake_b.detach(), "loss_d": loss_d.detach(), "loss_g_gan": loss_g_gan.detach(),
+                "loss_feat": loss_feat.detach(), "loss_tv": loss_tv.detach(), "loss_g": loss_g.detach()}

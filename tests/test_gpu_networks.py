@@ -1,0 +1,240 @@
+"""Whole-network and whole-step parity of the CUDA path (through the drop-in nn.Module API, which calls the
+C ABI) against the CPU oracle on the same seeded weights and inputs, plus the committed golden vectors that
+were generated from the unmodified reference.
+
+Tolerances (north star): fp32 verification mode -- outputs/losses within 1e-4 relative (1e-5 is met per
+kernel, see test_gpu_ops.py; 24 BatchNorm layers amplify rounding differences between summation orders);
+bf16 mode -- max error <= 1e-2 of the tensor's scale for the generator output and both losses.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import pix2pix_oracle as orc
+from oracle.make_golden_util import CASES
+
+DEV = "cuda"
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def relerr(a, b):
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    return (a - b).abs().max().item() / max(b.abs().max().item(), 1e-30)
+
+
+def rms_relerr(a, b):
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    return ((a - b).pow(2).mean().sqrt() / b.pow(2).mean().sqrt().clamp_min(1e-30)).item()
+
+
+def build(precision):
+    import p2p_pytorch_b200 as P
+    P.set_precision(precision)
+    g = P.ExpandNetwork().to(DEV)
+    d = P.MultiscaleDiscriminator(6, 64, getIntermFeat=True).to(DEV)
+    g.load_state_dict(orc.init_g_state(123))
+    d.load_state_dict(orc.init_d_state(124))
+    g.train(); d.train()
+    return P, g, d
+
+
+@pytest.fixture(autouse=True)
+def _restore_precision():
+    yield
+    import p2p_pytorch_b200 as P
+    P.set_precision("bf16")
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32", 2e-4), ("bf16-simt", 1.5e-2), ("bf16", 1.5e-2)])
+def test_generator_forward_backward(precision, tol):
+    P, g, _ = build(precision)
+    a, b, c = orc.synthetic_batch(2, 32, 32, 5)
+    og = orc.init_g_state(123)
+    for k in orc.g_trainable(og):
+        og[k].requires_grad_(True)
+    y_ref = orc.g_forward(og, c, True)
+    y = g(c.to(DEV))
+    assert y.shape == y_ref.shape and y.dtype == torch.float32
+    assert relerr(y, y_ref) <= tol, "generator output"
+    # BatchNorm running buffers follow the reference's update
+    sd = g.state_dict()
+    for k in ("in1_e.running_mean", "res5.in2.running_var", "in1_d.running_mean"):
+        assert relerr(sd[k], og[k]) <= max(tol, 1e-3), k
+    assert sd["in2_d.num_batches_tracked"].item() == 1
+    torch.manual_seed(0)
+    gy = torch.randn_like(y_ref)
+    y_ref.backward(gy)
+    y.backward(gy.to(DEV))
+    gtol = 2e-3 if precision == "fp32" else 6e-2
+    for name, p in g.named_parameters():
+        ref = og[name].grad
+        if name.endswith("conv2d.bias"):
+            continue            # analytically zero (BatchNorm follows): float noise on both sides
+        assert p.grad is not None, name
+        assert rms_relerr(p.grad, ref) <= gtol, f"grad {name}: {rms_relerr(p.grad, ref):.3e}"
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-4), ("bf16-simt", 1.5e-2), ("bf16", 1.5e-2)])
+def test_discriminator_forward_backward(precision, tol):
+    P, _, d = build(precision)
+    a, b, _ = orc.synthetic_batch(2, 32, 40, 9)
+    od = orc.init_d_state(124)
+    for k in orc.d_trainable(od):
+        od[k].requires_grad_(True)
+    xb = b.clone().requires_grad_(True)
+    ref = orc.d_forward(od, torch.cat((a, xb), 1))
+    xin = torch.cat((a, b), 1).to(DEV).requires_grad_(True)
+    out = d(xin)                                        # drop-in API: list[3][5] of NCHW fp32
+    assert len(out) == 3 and all(len(s) == 5 for s in out)
+    for i in range(3):
+        for j in range(5):
+            assert out[i][j].shape == ref[i][j].shape, (i, j)
+            assert relerr(out[i][j], ref[i][j]) <= tol, f"map {i}{j}"
+    # u, v were advanced by the power iteration exactly like the reference's
+    sd = d.state_dict()
+    for k in ("scale2_layer1.0.module.weight_u", "scale0_layer3.0.module.weight_v"):
+        assert relerr(sd[k], od[k]) <= 1e-4, k
+    loss_ref = orc.gan_loss(ref, True) + orc.feature_matching_loss(ref, [[torch.zeros_like(t) for t in s] for s in ref])
+    crit = P.GANLoss()
+    loss = crit(out, True)
+    for i in range(3):
+        for j in range(4):
+            loss = loss + (10.0 / 3) * out[i][j].abs().mean()
+    assert abs(loss.item() - loss_ref.item()) <= max(tol, 1e-4) * abs(loss_ref.item())
+    loss_ref.backward(); loss.backward()
+    gtol = 2e-3 if precision == "fp32" else 6e-2
+    for name, p in d.named_parameters():
+        if not p.requires_grad:
+            continue
+        assert p.grad is not None, name
+        assert rms_relerr(p.grad, od[name].grad) <= gtol, f"grad {name}: {rms_relerr(p.grad, od[name].grad):.3e}"
+    assert rms_relerr(xin.grad[:, 3:], xb.grad) <= gtol, "input gradient"
+
+
+def _run_trainer(precision, batch, h, w, seed, steps):
+    P, g, d = build(precision)
+    tr = P.Pix2PixTrainer(g, d)
+    outs = []
+    for it in range(steps):
+        a, b, c = orc.synthetic_batch(batch, h, w, seed + it)
+        outs.append({k: v.float().cpu() for k, v in tr.step(a.to(DEV), b.to(DEV), c.to(DEV)).items()})
+    return tr, g, d, outs
+
+
+@pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
+def test_train_step_fp32_matches_reference_golden(case):
+    """The committed golden vectors come from the unmodified reference (oracle/make_golden.py)."""
+    from oracle.make_golden_util import fingerprint
+    name, batch, h, w, steps, seed = case
+    gold = np.load(os.path.join(GOLD, f"ref_step_{name}.npz"))
+    tr, g, d, outs = _run_trainer("fp32", batch, h, w, seed, 1)
+    o = outs[0]
+    assert relerr(o["fake_b"], torch.from_numpy(gold["s0.fake_b"])) <= 2e-4
+    for nm in ("loss_d", "loss_g_gan", "loss_feat", "loss_tv", "loss_g"):
+        assert abs(o[nm].item() - float(gold["s0." + nm])) <= 2e-4 * abs(float(gold["s0." + nm])), nm
+    # weights after the two Adam steps, BatchNorm buffers, spectral-norm vectors
+    for net, pre in ((g, "s0.gstate."), (d, "s0.dstate.")):
+        for k, v in net.state_dict().items():
+            if k.endswith("conv2d.bias") or k.endswith("num_batches_tracked"):
+                continue
+            fp, ref = fingerprint(v.float().cpu()), gold[pre + k]
+            rms = max(float(np.sqrt(ref[2] / max(v.numel(), 1))), 1e-12)
+            assert np.abs(fp[3:] - ref[3:]).max() <= 5e-4 * rms + 4.1e-4, k      # 2*lr: Adam sign flips where |g|~eps
+            assert abs(fp[1] - ref[1]) <= 2e-3 * abs(ref[1]) + 1e-6, k
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32", 2e-4), ("bf16", 1.5e-2)])
+def test_train_step_matches_oracle(precision, tol):
+    tr, g, d, outs = _run_trainer(precision, 2, 32, 32, 21, 1)
+    ot = orc.OracleTrainer(orc.init_g_state(123), orc.init_d_state(124))
+    a, b, c = orc.synthetic_batch(2, 32, 32, 21)
+    ref = ot.step(a, b, c)
+    assert relerr(outs[0]["fake_b"], ref["fake_b"]) <= tol
+    for nm in ("loss_d", "loss_g_gan", "loss_feat", "loss_tv", "loss_g"):
+        assert abs(outs[0][nm].item() - ref[nm].item()) <= tol * abs(ref[nm].item()), nm
+    gg, dg = ot.grads()
+    gtol = 3e-3 if precision == "fp32" else 8e-2
+    for name, p in g.named_parameters():
+        if name.endswith("conv2d.bias"):
+            continue
+        assert rms_relerr(p.grad, gg[name]) <= gtol, f"G grad {name}: {rms_relerr(p.grad, gg[name]):.3e}"
+    for name, p in d.named_parameters():
+        if p.requires_grad:
+            assert rms_relerr(p.grad, dg[name]) <= gtol, f"D grad {name}: {rms_relerr(p.grad, dg[name]):.3e}"
+
+
+def test_drop_in_loop_equals_fused_trainer():
+    """train.py's loop typed against the drop-in modules (torch.cat, GANLoss, nn.L1Loss, torch.optim.Adam)
+    gives the same step as Pix2PixTrainer."""
+    P, g, d = build("fp32")
+    a, b, c = (t.to(DEV) for t in orc.synthetic_batch(2, 32, 32, 33))
+    crit, feat = P.GANLoss(), torch.nn.L1Loss()
+    opt_g = torch.optim.Adam(g.parameters(), lr=2e-4, betas=(0.5, 0.999))
+    opt_d = torch.optim.Adam(d.parameters(), lr=2e-4, betas=(0.5, 0.999))
+    fake_b = g(c)
+    pred_fake = d.forward(torch.cat((a, fake_b.detach()), 1))
+    loss_d_fake = crit(pred_fake, False)
+    pred_real = d.forward(torch.cat((a, b), 1))
+    loss_d = (loss_d_fake + crit(pred_real, True)) * 0.5
+    pred_fake = d.forward(torch.cat((a, fake_b), 1))
+    loss_g = crit(pred_fake, True)
+    for i in range(3):
+        for j in range(4):
+            loss_g = loss_g + (1.0 / 3) * feat(pred_fake[i][j], pred_real[i][j].detach()) * 10.0
+    loss_g = loss_g + P.tv_loss(fake_b)
+    opt_g.zero_grad(); loss_g.backward(); opt_g.step()
+    opt_d.zero_grad(); loss_d.backward(); opt_d.step()
+    _, g2, d2, outs = _run_trainer("fp32", 2, 32, 32, 33, 1)
+    assert relerr(fake_b, outs[0]["fake_b"]) <= 1e-5
+    assert abs(loss_d.item() - outs[0]["loss_d"].item()) <= 1e-5 * abs(loss_d.item())
+    assert abs(loss_g.item() - outs[0]["loss_g"].item()) <= 1e-5 * abs(loss_g.item())
+    for (k, v), (_, v2) in zip(g.state_dict().items(), g2.state_dict().items()):
+        if k.endswith("conv2d.bias"):
+            continue
+        assert (v.float() - v2.float()).abs().max().item() <= 4.1e-4, k
+    for (k, v), (_, v2) in zip(d.state_dict().items(), d2.state_dict().items()):
+        assert (v.float() - v2.float()).abs().max().item() <= 4.1e-4, k
+
+
+def test_state_dict_interchange_and_eval_mode():
+    P, g, d = build("fp32")
+    assert list(g.state_dict().keys()) == list(orc.init_g_state().keys())
+    assert list(d.state_dict().keys()) == list(orc.init_d_state().keys())
+    g.eval()
+    _, _, c = orc.synthetic_batch(1, 32, 32, 2)
+    with torch.no_grad():
+        y = g(c.to(DEV))
+    og = orc.init_g_state(123)
+    assert relerr(y, orc.g_forward(og, c, False)) <= 2e-4
+    assert g.state_dict()["in1_e.num_batches_tracked"].item() == 0
+    with pytest.raises(Exception):
+        g(torch.zeros(1, 3, 30, 32, device=DEV))          # H not a multiple of 4
+    with pytest.raises(Exception):
+        g(torch.zeros(1, 3, 32, 32))                      # CPU tensor: no fallback path
+
+
+def test_loss_curves_track_oracle_200_steps():
+    """north star: loss curves track the reference over 200 steps (fp32 verification mode, batch 2, 32x32)."""
+    steps = 200
+    P, g, d = build("fp32")
+    tr = P.Pix2PixTrainer(g, d)
+    ot = orc.OracleTrainer(orc.init_g_state(123), orc.init_d_state(124))
+    mine, ref = [], []
+    for it in range(steps):
+        a, b, c = orc.synthetic_batch(2, 32, 32, 1000 + it)
+        o = tr.step(a.to(DEV), b.to(DEV), c.to(DEV))
+        r = ot.step(a, b, c)
+        mine.append([o[k].item() for k in ("loss_d", "loss_g")])
+        ref.append([r[k].item() for k in ("loss_d", "loss_g")])
+    mine, ref = np.array(mine), np.array(ref)
+    os.makedirs("gpurun_out", exist_ok=True)
+    np.savez("gpurun_out/loss_curves_200.npz", mine=mine, ref=ref)
+    # window means: Adam amplifies last-bit differences, so the curves are compared smoothed, not pointwise
+    for lo in range(0, steps, 25):
+        m, r = mine[lo:lo + 25].mean(0), ref[lo:lo + 25].mean(0)
+        assert np.all(np.abs(m - r) <= 0.05 * np.abs(r) + 1e-3), (lo, m, r)
+    assert np.all(np.abs(mine[:5] - ref[:5]) <= 2e-3 * np.abs(ref[:5]) + 1e-5)
