@@ -29,23 +29,25 @@ class FusedAdam(torch.optim.Optimizer):
             L.require_cuda(p, "parameter")
             if p.dtype != torch.float32 or p.device != dev:
                 raise ValueError("FusedAdam needs fp32 parameters on one device")
-        n = sum(p.numel() for p in self._ps)
+        # every parameter starts on a 32-byte boundary of the flat buffer (vector loads in the kernels that read
+        # weights in place, e.g. the spectral-norm matvec); the gaps stay zero in p, g, m and v forever
+        self._offsets, n = [], 0
+        for p in self._ps:
+            self._offsets.append(n)
+            n += (p.numel() + 7) // 8 * 8
         self.numel = n
         self.flat_p = torch.empty(n, dtype=torch.float32, device=dev)
         self.flat_g = torch.zeros(n, dtype=torch.float32, device=dev)
         self.exp_avg = torch.zeros(n, dtype=torch.float32, device=dev)
         self.exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=dev)
-        self._offsets = []
-        off = 0
+        self.flat_p.zero_()
         with torch.no_grad():
-            for p in self._ps:
+            for p, off in zip(self._ps, self._offsets):
                 k = p.numel()
                 view = self.flat_p[off:off + k].view(p.shape)
                 view.copy_(p.data)
                 p.data = view
                 p.grad = self.flat_g[off:off + k].view(p.shape)
-                self._offsets.append(off)
-                off += k
         self.steps = 0
         self.grad_scale = 1.0   # set to 1/world_size by the data-parallel trainer (all-reduce is a sum)
 

@@ -19,6 +19,9 @@ def _pkg():
     import p2p_pytorch_b200 as P_
     from p2p_pytorch_b200 import _lib as L_, engine as E_
     P, L, E = P_, L_, E_
+    # the torch references below must be true fp32 (cuDNN / cuBLAS default to TF32 for fp32 convs and matmuls)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
     yield
 
 
