@@ -3,6 +3,7 @@ fp32 kernels: max |err| <= 1e-5 of the output scale (the north star's fp32 verif
 bf16 / tcgen05 kernels: <= 1e-2 of the output scale against a reference fed the same bf16-rounded inputs."""
 import ctypes as C
 import math
+import zlib
 
 import pytest
 import torch
@@ -60,7 +61,7 @@ CONV_CASES = [
 
 def _conv_case(case, dt, impl, tol):
     name, B, cin, cout, H, W, k, s, pad = case
-    g = torch.Generator(device="cpu").manual_seed(hash(name) % 1000)
+    g = torch.Generator(device="cpu").manual_seed(zlib.crc32(name.encode()) % 1000)
     x = torch.randn(B, cin, H, W, generator=g).to(DEV)
     w = (torch.randn(cout, cin, k, k, generator=g) / math.sqrt(cin * k * k)).to(DEV)
     bias = torch.randn(cout, generator=g).to(DEV)
@@ -75,9 +76,11 @@ def _conv_case(case, dt, impl, tol):
         stats = torch.zeros(2 * Co, dtype=torch.float64, device=DEV)
         plan.fwd(xs, bias, out, stats)
         # reference on the same (rounded) operands
-        xr = from_stored(xs, cin).requires_grad_(True)
-        wr = w.to(dt).float().requires_grad_(True)
-        ref = F.conv2d(xr, wr, bias, stride=s, padding=pad)
+        # fp32 kernels are held to 1e-5 against an fp64 reference (two fp32 summation orders differ by more)
+        rdt = torch.float64 if dt == torch.float32 else torch.float32
+        xr = from_stored(xs, cin).to(rdt).requires_grad_(True)
+        wr = w.to(dt).to(rdt).requires_grad_(True)
+        ref = F.conv2d(xr, wr, bias.to(rdt), stride=s, padding=pad)
         got = from_stored(out, cout)
         assert relerr(got, ref) <= tol, f"{name} fwd"
         assert out[..., cout:].abs().max().item() == 0 if Co > cout else True
@@ -89,7 +92,7 @@ def _conv_case(case, dt, impl, tol):
         go = torch.randn(ref.shape, generator=g).to(DEV)
         gos = to_stored(go, Co, dt)
         gor = from_stored(gos, cout)
-        ref.backward(gor)
+        ref.backward(gor.to(rdt))
         din = torch.empty_like(xs)
         plan.dgrad(gos, din)
         assert relerr(from_stored(din, cin), xr.grad) <= tol, f"{name} dgrad"
