@@ -99,6 +99,24 @@ int p2p_spectral_norm(int n_layers, const float* const* w_host, float* const* u_
                       float* const* sigma_host, const int32_t* rows_host, const int32_t* cols_host, float* tmp,
                       void* stream);
 
+/* Allocation-free variant of p2p_spectral_norm.  It has no counterpart in the reference; it exists for
+ * callers that cannot allocate device memory when they run the discriminator: hosts that were given a fixed
+ * memory budget and laid out all their buffers in advance, and latency-sensitive loops where a
+ * cudaMalloc/cudaFree pair would synchronise the device in the middle of a step.  Same arguments and results
+ * as p2p_spectral_norm, minus `tmp`: the scratch is a static array inside the library, held by every GPU that
+ * loads the library until the process exits (P2P_SN_STATIC_MAX_FLOATS floats = 128 KiB).
+ *   - sum(rows + cols) over the layers must not exceed P2P_SN_STATIC_MAX_FLOATS (define_D needs 24,192);
+ *     larger requests are rejected (<0, see p2p_last_error()) -- use p2p_spectral_norm with your own buffer;
+ *   - the first call on each device looks up the array's device address; make that first call before
+ *     starting any stream capture on that device.  No call allocates or frees memory;
+ *   - all calls share the one array, and it keeps whatever the previous call left in it (the kernels
+ *     overwrite every element before reading it, so nothing needs clearing).  Two calls whose kernels can
+ *     overlap on the GPU -- different streams, or different host threads -- race on it: serialise them. */
+#define P2P_SN_STATIC_MAX_FLOATS 32768
+int p2p_spectral_norm_static(int n_layers, const float* const* w_host, float* const* u_host, float* const* v_host,
+                             float* const* sigma_host, const int32_t* rows_host, const int32_t* cols_host,
+                             void* stream);
+
 /* ---- generator glue: pixel-unshuffle / upsample / reflection pad / BatchNorm / activations --- */
 
 /* x NCHW fp32 [B,3,H,W] -> conv1 input [B,H+8,W+8,16]: PixelUnshuffle(2) + nearest x2 + ReflectionPad(4)

@@ -41,6 +41,7 @@ SIGNATURES = {
     "p2p_unpack_wgrad": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp],
     "p2p_sn_weight_grad": [_vp, _vp, _vp, _vp, _vp, _i, _i, _vp],
     "p2p_spectral_norm": [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
+    "p2p_spectral_norm_static": [_i, _vp, _vp, _vp, _vp, _vp, _vp, _vp],
     "p2p_g_input_prep": [_vp, _vp, _i, _i, _i, _i, _vp],
     "p2p_channel_stats": [_vp, _vp, _i64, _i, _i, _vp],
     "p2p_bn_finalize": [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],

@@ -1,6 +1,8 @@
 // Parameter-side kernels: weight packing for the two GEMM operand layouts, gradient unpacking into
 // PyTorch's [co][ci][kh][kw] parameter layout, and the hand-rolled SpectralNorm of the reference
 // (networks.py:525-582): one power iteration per forward, W = W_bar / sigma, sigma differentiable in W_bar.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace p2p {
@@ -206,3 +208,62 @@ int p2p_spectral_norm(int n_layers, const float* const* w_host, float* const* u_
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------
+// Allocation-free variant of the power iteration.
+//
+// p2p_spectral_norm needs sum(rows + cols) floats of scratch that its caller has to provide, i.e. allocate.
+// Some callers of this library cannot allocate device memory at the point where they run the
+// discriminator: a host program that was handed a fixed memory budget and carved all of its buffers out
+// up front (serving loops, embedded trainers), and latency-sensitive loops in which a cudaMalloc/cudaFree
+// pair would synchronise the whole device in the middle of a step.  For them the scratch below is part of
+// the library image itself: a fixed-size array in device memory that every GPU which loads the library
+// holds from load until the process exits.
+//
+// g_sn_scratch as written in HOST code is only the host-side handle of the symbol -- it is not a device
+// address and must never be handed to a kernel.  The device address is looked up once per device with
+// cudaGetSymbolAddress (with that device current) and cached.
+// ---------------------------------------------------------------------------------------------------
+static __device__ __align__(256) float g_sn_scratch[P2P_SN_STATIC_MAX_FLOATS];
+
+namespace p2p {
+constexpr int kMaxDevices = 64;
+static float* g_sn_scratch_addr[kMaxDevices] = {};
+static std::mutex g_sn_scratch_mutex;
+
+// device address of g_sn_scratch on the current device; the first call per device resolves it
+static int sn_static_scratch(float** out) {
+  int dev = -1;
+  P2P_CUDA(cudaGetDevice(&dev));
+  P2P_REQUIRE(dev >= 0 && dev < kMaxDevices, "device ordinal out of range");
+  std::lock_guard<std::mutex> lock(g_sn_scratch_mutex);
+  if (g_sn_scratch_addr[dev] == nullptr) {
+    float* p = nullptr;
+    P2P_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_sn_scratch));
+    P2P_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null address");
+    g_sn_scratch_addr[dev] = p;
+  }
+  *out = g_sn_scratch_addr[dev];
+  return 0;
+}
+}  // namespace p2p
+
+extern "C" int p2p_spectral_norm_static(int n_layers, const float* const* w_host, float* const* u_host,
+                                        float* const* v_host, float* const* sigma_host, const int32_t* rows_host,
+                                        const int32_t* cols_host, void* stream) {
+  P2P_REQUIRE(n_layers >= 1 && n_layers <= P2P_SN_MAX_LAYERS, "1..16 layers per call");
+  P2P_REQUIRE(rows_host && cols_host, "null pointer");
+  long long need = 0;
+  for (int l = 0; l < n_layers; ++l) {
+    P2P_REQUIRE(rows_host[l] > 0 && cols_host[l] > 0, "empty weight matrix");
+    need += (long long)rows_host[l] + cols_host[l];
+  }
+  P2P_REQUIRE(need <= P2P_SN_STATIC_MAX_FLOATS,
+              "sum(rows + cols) = " + std::to_string(need) + " floats exceeds the built-in scratch of " +
+                  std::to_string(P2P_SN_STATIC_MAX_FLOATS) + " floats: use p2p_spectral_norm with your own buffer");
+  float* scratch = nullptr;
+  if (int e = sn_static_scratch(&scratch)) return e;
+  // Nothing in the scratch has to start at zero: every element a kernel reads was written earlier in the
+  // same call (W^T u fills [0, cols), W v fills [cols, cols + rows) of each layer's slice).
+  return p2p_spectral_norm(n_layers, w_host, u_host, v_host, sigma_host, rows_host, cols_host, scratch, stream);
+}
