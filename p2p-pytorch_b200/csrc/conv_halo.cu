@@ -1,0 +1,342 @@
+// Halo-resident tcgen05 implicit-GEMM convolution for stride-1 problems (forward of the stride-1 layers and
+// every data-gradient), sm_100a.  Reference layers: networks.py:404 (ConvLayer), :422 (UpsampleConvLayer),
+// :776-784 (the stride-1 D convs), and autograd's conv backward-data for all of them.
+//
+// conv_tc.cu re-reads the input from L2 once per filter tap.  Here one TMA 4-D box brings the whole input
+// halo of a 32x8-pixel output block (two 16x8 = 128-row UMMA tiles) into shared memory ONCE per 64-channel
+// chunk, and every tap is just a different UMMA descriptor into that tile:
+//     row(m, tap) = (m/8 + dh)*HW + (m%8 + dw)          start address = base + row*pitch, SBO = HW*pitch
+// which works because tcgen05.mma applies the shared-memory swizzle to absolute address bits (probed on
+// hardware: tools/probe/umma_shift_probe.cu -- row-shifted starts and SBO != 8 rows give exact results).
+// Only the weights still stream per (tap, chunk), and each weight tile feeds two accumulator tiles, so the
+// L2->SM traffic per 128 output pixels drops from 576 KB to ~190 KB for the 3x3 128->128 layer.
+//
+// Persistent kernel, one CTA per SM, 7 warps:  warp 0 = halo (A) TMA producer, warp 6 = weight (B) TMA
+// producer, warp 1 = MMA issuer, warps 2-5 = epilogue.  TMEM holds two accumulator sets (2 tiles x BLOCK_N
+// columns each), so the epilogue of block i overlaps the MMAs of block i+1.
+#include "tc_common.cuh"
+
+namespace p2p {
+
+using namespace tc;
+
+constexpr int kHaloMaxTaps = 81;
+
+struct HaloTap {
+  int16_t row_off;  // (dh - min_dh) * HW + (dw - min_dw)
+  int16_t pad_;
+  int32_t wk;       // first K index of this tap in the weight matrix
+};
+
+struct HaloParams {
+  int n_taps, c_chunks, n_tiles;        // K loop; output-channel tiles
+  int blocks_w, blocks_h, n_img;        // 32x8 pixel blocks per image
+  int min_dh, min_dw, HW, HH;           // halo geometry (halo is HH x HW pixels)
+  int a_bytes;                          // bytes of one halo chunk buffer (1024-aligned)
+  int nb;                               // weight ring depth
+  int Hv, Wv;                           // valid output-position grid
+  int64_t out_sN, out_sH, out_sW;
+  int h_mul, h_off, w_mul, w_off;
+  int co_real, act, Cn;
+  __nv_bfloat16* out;
+  const float* bias;
+  double* stats;
+  HaloTap taps[kHaloMaxTaps];
+};
+
+template <int BLOCK_N, int CIN_BLK>
+__global__ void __launch_bounds__(224, 1)
+    conv_halo_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                     const __grid_constant__ HaloParams p) {
+  constexpr int RB = CIN_BLK * 2;                 // bytes per halo row (= swizzle span)
+  constexpr int B_BYTES = BLOCK_N * RB;           // one weight tile
+  constexpr int PITCH = BLOCK_N * 2 + 16;         // epilogue staging row pitch
+  constexpr int NA = 2;
+  constexpr uint32_t TMEM_COLS = 4 * BLOCK_N < 32 ? 32 : 4 * BLOCK_N;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = sA + NA * p.a_bytes;
+  uint8_t* stg = sB + p.nb * B_BYTES;
+  __shared__ uint64_t a_full[NA], a_empty[NA], b_full[8], b_empty[8], t_full[2], t_empty[2];
+  __shared__ uint32_t tmem_base_s;
+  __shared__ float s_bias[BLOCK_N];
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int blocks_per_img = p.blocks_w * p.blocks_h;
+  const int items_per_ntile = blocks_per_img * p.n_img;
+  const int n_items = items_per_ntile * p.n_tiles;
+
+  if (threadIdx.x == 0) {
+    prefetch_tmap(&map_a);
+    prefetch_tmap(&map_b);
+    for (int s = 0; s < NA; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); }
+    for (int s = 0; s < p.nb; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&t_full[s], 1); mbar_init(&t_empty[s], 4); }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc(&tmem_base_s, TMEM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_s;
+
+  if (threadIdx.x == 0) {
+    // ===== halo producer: one box per (item, channel chunk) =====
+    int ab = 0;
+    uint32_t aph = 0;
+    for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+      const int r = it % items_per_ntile;
+      const int img = r / blocks_per_img, br = r % blocks_per_img;
+      const int oy0 = (br / p.blocks_w) * 32, ox0 = (br % p.blocks_w) * 8;
+      for (int c = 0; c < p.c_chunks; ++c) {
+        mbar_wait(&a_empty[ab], aph ^ 1);
+        mbar_arrive_expect_tx(&a_full[ab], (uint32_t)(p.HH * p.HW * RB));
+        tma_load_4d(sA + ab * p.a_bytes, &map_a, &a_full[ab], c * CIN_BLK, ox0 + p.min_dw, oy0 + p.min_dh, img);
+        if (++ab == NA) { ab = 0; aph ^= 1; }
+      }
+    }
+  } else if (threadIdx.x == 192) {
+    // ===== weight producer: one tile per (item, chunk, tap) =====
+    int bs = 0;
+    uint32_t bph = 0;
+    for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+      const int n0 = (it / items_per_ntile) * BLOCK_N;
+      for (int c = 0; c < p.c_chunks; ++c)
+        for (int t = 0; t < p.n_taps; ++t) {
+          mbar_wait(&b_empty[bs], bph ^ 1);
+          mbar_arrive_expect_tx(&b_full[bs], B_BYTES);
+          tma_load_2d(sB + bs * B_BYTES, &map_b, &b_full[bs], p.taps[t].wk + c * CIN_BLK, n0);
+          if (++bs == p.nb) { bs = 0; bph ^= 1; }
+        }
+    }
+  } else if (threadIdx.x == 32) {
+    // ===== MMA issuer =====
+    constexpr uint32_t idesc = umma_idesc_bf16(128, BLOCK_N, 0, 0);
+    const uint32_t sbo_field = (uint32_t)((p.HW * RB) >> 4) & 0x3FFF;
+    int ab = 0, bs = 0, li = 0;
+    uint32_t aph = 0, bph = 0;
+    for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++li) {
+      const int set = li & 1;
+      mbar_wait(&t_empty[set], ((li >> 1) & 1) ^ 1);
+      tc_fence_after();
+      const uint32_t acc = tmem_base + set * 2 * BLOCK_N;
+      for (int c = 0; c < p.c_chunks; ++c) {
+        mbar_wait(&a_full[ab], aph);
+        const uint32_t a_base = smem_u32(sA + ab * p.a_bytes);
+        for (int t = 0; t < p.n_taps; ++t) {
+          mbar_wait(&b_full[bs], bph);
+          tc_fence_after();
+          const uint32_t b_base = smem_u32(sB + bs * B_BYTES);
+          const uint32_t a_tap = a_base + (uint32_t)p.taps[t].row_off * RB;
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+#pragma unroll
+            for (int k = 0; k < CIN_BLK / 16; ++k) {
+              uint64_t ad = smem_desc_kmajor(a_tap + h * 16 * p.HW * RB + k * 32, RB);
+              ad = (ad & ~(uint64_t(0x3FFF) << 32)) | ((uint64_t)sbo_field << 32);   // 8-row groups are HW rows apart
+              umma_bf16(acc + h * BLOCK_N, ad, smem_desc_kmajor(b_base + k * 32, RB), idesc, (c | t | k) != 0 ? 1u : 0u);
+            }
+          }
+          umma_commit(&b_empty[bs]);
+          if (++bs == p.nb) { bs = 0; bph ^= 1; }
+        }
+        umma_commit(&a_empty[ab]);
+        if (++ab == NA) { ab = 0; aph ^= 1; }
+      }
+      umma_commit(&t_full[set]);
+    }
+  } else if (warp >= 2 && warp <= 5) {
+    // ===== epilogue =====
+    const int q = warp & 3;
+    const int row = q * 32 + lane;          // accumulator row = pixel (row/8, row%8) of the 16x8 tile
+    const int et = threadIdx.x - 64;        // 0..127
+    int li = 0;
+    int cur_n0 = -1;
+    for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++li) {
+      const int set = li & 1;
+      const int n0 = (it / items_per_ntile) * BLOCK_N;
+      const int r = it % items_per_ntile;
+      const int img = r / blocks_per_img, br = r % blocks_per_img;
+      const int oy0 = (br / p.blocks_w) * 32, ox0 = (br % p.blocks_w) * 8;
+      if (n0 != cur_n0) {
+        named_bar_sync(1, 128);
+        for (int i = et; i < BLOCK_N; i += 128)
+          s_bias[i] = (p.bias != nullptr && n0 + i < p.co_real) ? p.bias[n0 + i] : 0.f;
+        named_bar_sync(1, 128);
+        cur_n0 = n0;
+      }
+      mbar_wait(&t_full[set], (li >> 1) & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int h = 0; h < 2; ++h) {
+        const int ty = h * 16 + (row >> 3), tx = row & 7;
+        const bool valid = (oy0 + ty) < p.Hv && (ox0 + tx) < p.Wv;
+        constexpr int CH = BLOCK_N >= 32 ? 32 : 16;
+#pragma unroll 1
+        for (int c0 = 0; c0 < BLOCK_N; c0 += CH) {
+          uint32_t v[32];
+          const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(set * 2 * BLOCK_N + h * BLOCK_N + c0);
+          if (CH == 32) tmem_ld32(taddr, v); else tmem_ld16(taddr, v);
+          tmem_ld_wait();
+          uint32_t pk[CH / 2];
+#pragma unroll
+          for (int j = 0; j < CH; j += 2) {
+            float f0 = __uint_as_float(v[j]) + s_bias[c0 + j];
+            float f1 = __uint_as_float(v[j + 1]) + s_bias[c0 + j + 1];
+            if (p.act == P2P_ACT_LRELU) {
+              f0 = f0 > 0.f ? f0 : 0.2f * f0;
+              f1 = f1 > 0.f ? f1 : 0.2f * f1;
+            }
+            if (!valid || n0 + c0 + j >= p.co_real) f0 = 0.f;
+            if (!valid || n0 + c0 + j + 1 >= p.co_real) f1 = 0.f;
+            pk[j / 2] = pack_bf16x2(f0, f1);
+          }
+          uint4* dst = reinterpret_cast<uint4*>(stg + row * PITCH + c0 * 2);
+#pragma unroll
+          for (int j = 0; j < CH / 8; ++j) dst[j] = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+        }
+        if (h == 1) {
+          // both tiles of this accumulator set are in registers / staging: hand the set back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&t_empty[set]);
+        }
+        named_bar_sync(1, 128);
+        if (p.stats != nullptr) {
+          for (int c = et; c < BLOCK_N; c += 128) {
+            if (n0 + c < p.co_real) {
+              float s = 0.f, ss = 0.f;
+#pragma unroll 8
+              for (int rr = 0; rr < 128; ++rr) {
+                const float f = __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(stg + rr * PITCH + c * 2));
+                s += f;
+                ss = fmaf(f, f, ss);
+              }
+              atomicAdd(p.stats + n0 + c, (double)s);
+              atomicAdd(p.stats + p.Cn + n0 + c, (double)ss);
+            }
+          }
+        }
+        constexpr int LPR = BLOCK_N / 8;   // lanes per pixel row (16 B each)
+        constexpr int RPI = 128 / LPR;
+        const int sub = et % LPR, r_in = et / LPR;
+#pragma unroll 1
+        for (int r0 = 0; r0 < 128; r0 += RPI) {
+          const int rr = r0 + r_in;
+          const int yy = oy0 + h * 16 + (rr >> 3), xx = ox0 + (rr & 7);
+          if (yy < p.Hv && xx < p.Wv) {
+            const uint4 val = *reinterpret_cast<const uint4*>(stg + rr * PITCH + sub * 16);
+            __nv_bfloat16* o = p.out + (int64_t)img * p.out_sN + (int64_t)(yy * p.h_mul + p.h_off) * p.out_sH +
+                               (int64_t)(xx * p.w_mul + p.w_off) * p.out_sW + n0 + sub * 8;
+            *reinterpret_cast<uint4*>(o) = val;
+          }
+        }
+        named_bar_sync(1, 128);   // staging is reused by the next tile
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------
+template <int BLOCK_N, int CIN_BLK>
+static int launch_halo(const CUtensorMap& ma, const CUtensorMap& mb, const HaloParams& p, int grid, int smem,
+                       cudaStream_t st) {
+  static int attr_smem = 0;
+  if (smem > attr_smem) {
+    P2P_CUDA(cudaFuncSetAttribute(conv_halo_kernel<BLOCK_N, CIN_BLK>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_smem = smem;
+  }
+  conv_halo_kernel<BLOCK_N, CIN_BLK><<<grid, 224, smem, st>>>(ma, mb, p);
+  P2P_LAUNCH_CHECK();
+}
+
+template <int CIN_BLK>
+static int launch_halo_n(int block_n, const CUtensorMap& ma, const CUtensorMap& mb, const HaloParams& p, int grid,
+                         int smem, cudaStream_t st) {
+  switch (block_n) {
+    case 16: return launch_halo<16, CIN_BLK>(ma, mb, p, grid, smem, st);
+    case 32: return launch_halo<32, CIN_BLK>(ma, mb, p, grid, smem, st);
+    case 64: return launch_halo<64, CIN_BLK>(ma, mb, p, grid, smem, st);
+    default: return launch_halo<128, CIN_BLK>(ma, mb, p, grid, smem, st);
+  }
+}
+
+// A stride-1 implicit-GEMM problem.  taps: (dh, dw, wk) triples.  Returns -2 when the shape does not fit
+// (the caller then uses the per-tap kernel of conv_tc.cu).
+int run_halo_problem(const void* a_src, int N, int Hs, int Ws, int Ck, const void* b_mat, int Cn, int64_t ktot,
+                     const int* dh, const int* dw, const int* wk, int n_taps, int Hv, int Wv, __nv_bfloat16* out,
+                     int64_t out_sN, int64_t out_sH, int64_t out_sW, int h_mul, int h_off, int w_mul, int w_off,
+                     int co_real, int act, const float* bias, double* stats, cudaStream_t st) {
+  if (n_taps > kHaloMaxTaps) return -2;
+  const int cin_blk = Ck >= 64 ? 64 : Ck;
+  const int block_n = Cn >= 128 ? 128 : Cn;
+  const int rb = cin_blk * 2;
+  int mn_h = dh[0], mx_h = dh[0], mn_w = dw[0], mx_w = dw[0];
+  for (int t = 1; t < n_taps; ++t) {
+    mn_h = dh[t] < mn_h ? dh[t] : mn_h; mx_h = dh[t] > mx_h ? dh[t] : mx_h;
+    mn_w = dw[t] < mn_w ? dw[t] : mn_w; mx_w = dw[t] > mx_w ? dw[t] : mx_w;
+  }
+  HaloParams p{};
+  p.HW = 8 + (mx_w - mn_w);
+  p.HH = 32 + (mx_h - mn_h);
+  if (p.HW > 256 || p.HH > 256) return -2;
+  p.min_dh = mn_h;
+  p.min_dw = mn_w;
+  p.a_bytes = ((p.HH * p.HW * rb + 1023) / 1024) * 1024;
+  const int b_bytes = block_n * rb;
+  const int stg_bytes = 128 * (block_n * 2 + 16);
+  int nb = (48 * 1024) / b_bytes;
+  nb = nb > 8 ? 8 : nb;
+  int smem = 2 * p.a_bytes + nb * b_bytes + stg_bytes + 1024;
+  while (smem > 225 * 1024 && nb > 2) { --nb; smem -= b_bytes; }
+  if (smem > 225 * 1024) return -2;
+  p.nb = nb;
+  p.n_taps = n_taps;
+  for (int t = 0; t < n_taps; ++t) {
+    const int ro = (dh[t] - mn_h) * p.HW + (dw[t] - mn_w);
+    if (ro > 32767) return -2;
+    p.taps[t].row_off = (int16_t)ro;
+    p.taps[t].wk = wk[t];
+  }
+  p.c_chunks = Ck / cin_blk;
+  p.n_tiles = Cn / block_n;
+  p.blocks_w = (Wv + 7) / 8;
+  p.blocks_h = (Hv + 31) / 32;
+  p.n_img = N;
+  p.Hv = Hv; p.Wv = Wv;
+  p.out_sN = out_sN; p.out_sH = out_sH; p.out_sW = out_sW;
+  p.h_mul = h_mul; p.h_off = h_off; p.w_mul = w_mul; p.w_off = w_off;
+  p.co_real = co_real; p.act = act; p.Cn = Cn;
+  p.out = out; p.bias = bias; p.stats = stats;
+
+  CUtensorMap ma, mb;
+  {
+    const uint64_t dims[4] = {(uint64_t)Ck, (uint64_t)Ws, (uint64_t)Hs, (uint64_t)N};
+    const uint64_t strides[3] = {(uint64_t)Ck * 2, (uint64_t)Ws * Ck * 2, (uint64_t)Hs * Ws * Ck * 2};
+    const uint32_t box[4] = {(uint32_t)cin_blk, (uint32_t)p.HW, (uint32_t)p.HH, 1};
+    const uint32_t es[4] = {1, 1, 1, 1};
+    if (int e = make_map_bf16(&ma, a_src, 4, dims, strides, box, es, rb)) return e;
+  }
+  {
+    const uint64_t dims[2] = {(uint64_t)ktot, (uint64_t)Cn};
+    const uint64_t strides[1] = {(uint64_t)ktot * 2};
+    const uint32_t box[2] = {(uint32_t)cin_blk, (uint32_t)block_n};
+    const uint32_t es[2] = {1, 1};
+    if (int e = make_map_bf16(&mb, b_mat, 2, dims, strides, box, es, rb)) return e;
+  }
+  const int n_items = p.blocks_w * p.blocks_h * N * p.n_tiles;
+  const int grid = n_items < kSMs ? n_items : kSMs;
+  switch (cin_blk) {
+    case 16: return launch_halo_n<16>(block_n, ma, mb, p, grid, smem, st);
+    case 32: return launch_halo_n<32>(block_n, ma, mb, p, grid, smem, st);
+    default: return launch_halo_n<64>(block_n, ma, mb, p, grid, smem, st);
+  }
+}
+
+}  // namespace p2p

@@ -253,8 +253,31 @@ static int launch_n(int block_n, const CUtensorMap& ma, const CUtensorMap& mb, c
 }
 
 // One implicit-GEMM problem: A source tensor [N,Hs,Ws,Ck], B matrix [Cn][ktot], output positions Hv x Wv.
+// conv_halo.cu
+int run_halo_problem(const void* a_src, int N, int Hs, int Ws, int Ck, const void* b_mat, int Cn, int64_t ktot,
+                     const int* dh, const int* dw, const int* wk, int n_taps, int Hv, int Wv, __nv_bfloat16* out,
+                     int64_t out_sN, int64_t out_sH, int64_t out_sW, int h_mul, int h_off, int w_mul, int w_off,
+                     int co_real, int act, const float* bias, double* stats, cudaStream_t st);
+
+static bool g_use_halo = true;   // P2P_NO_HALO=1 forces the per-tap kernel (A/B comparisons)
+
 static int run_problem(const void* a_src, int N, int Hs, int Ws, int Ck, const void* b_mat, int Cn, int64_t ktot,
                        TcConvParams& p, cudaStream_t st) {
+  static bool env_checked = false;
+  if (!env_checked) {
+    const char* e = getenv("P2P_NO_HALO");
+    g_use_halo = !(e != nullptr && e[0] == '1');
+    env_checked = true;
+  }
+  if (p.in_mul == 1 && g_use_halo) {
+    // stride-1 problem: halo-resident kernel (one input read per channel chunk instead of one per tap)
+    int dh[kMaxTaps], dw[kMaxTaps], wk[kMaxTaps];
+    for (int t = 0; t < p.n_taps; ++t) { dh[t] = p.taps[t].dh; dw[t] = p.taps[t].dw; wk[t] = p.taps[t].wk; }
+    const int rc = run_halo_problem(a_src, N, Hs, Ws, Ck, b_mat, Cn, ktot, dh, dw, wk, p.n_taps, p.Hv, p.Wv, p.out,
+                                    p.out_sN, p.out_sH, p.out_sW, p.h_mul, p.h_off, p.w_mul, p.w_off, p.co_real, p.act,
+                                    p.bias, p.stats, st);
+    if (rc != -2) return rc;
+  }
   const int cin_blk = Ck >= 64 ? 64 : Ck;
   const int block_n = Cn >= 256 ? 256 : Cn;
   int tw;

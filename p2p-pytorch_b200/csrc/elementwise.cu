@@ -49,7 +49,7 @@ __global__ void __launch_bounds__(256) channel_stats_kernel(const T* __restrict_
   for (int k = 0; k < 8; ++k) s[k] = q[k] = 0.f;
   for (int64_t p = (int64_t)blockIdx.x * ppb + lane_p; p < pixels; p += (int64_t)gridDim.x * ppb) {
     float v[8];
-    ld8(r + p * C + c8 * 8, v);
+    ld8(r + (size_t)p * C + c8 * 8, v);
 #pragma unroll
     for (int k = 0; k < 8; ++k) { s[k] += v[k]; q[k] += v[k] * v[k]; }
   }
@@ -129,13 +129,13 @@ __global__ void bn_act_store_kernel(const T* __restrict__ r, const float* __rest
   const int C8 = C >> 3, Hu = H * up, Wu = W * up, Hd = Hu + 2 * pad, Wd = Wu + 2 * pad;
   const int sh = up == 2 ? 1 : 0;
   const float a = prelu_a != nullptr ? *prelu_a : 0.f;
-  const int64_t total = (int64_t)B * Hd * Wd * C8;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int c8 = (int)(i % C8);
-    int64_t p = i / C8;
-    const int dx = (int)(p % Wd); p /= Wd;
-    const int dy = (int)(p % Hd);
-    const int n = (int)(p / Hd);
+  const uint32_t total = (uint32_t)B * Hd * Wd * C8;   // < 2^31, checked by the caller
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % (uint32_t)C8);
+    uint32_t p = i / (uint32_t)C8;
+    const int dx = (int)(p % (uint32_t)Wd); p /= (uint32_t)Wd;
+    const int dy = (int)(p % (uint32_t)Hd);
+    const int n = (int)(p / (uint32_t)Hd);
     const int sy = reflect_idx(dy - pad, Hu) >> sh, sx = reflect_idx(dx - pad, Wu) >> sh;
     float v[8];
     ld8(r + (((int64_t)n * H + sy) * W + sx) * C + c8 * 8, v);
@@ -149,7 +149,7 @@ __global__ void bn_act_store_kernel(const T* __restrict__ r, const float* __rest
       if (skip != nullptr) z += sk[k];
       v[k] = act_fwd(z, act, a);
     }
-    st8(dst + i * 8, v);
+    st8(dst + (size_t)i * 8, v);
   }
 }
 
@@ -173,12 +173,10 @@ __global__ void bn_act_store_nchw_kernel(const T* __restrict__ r, const float* _
 }
 
 // rows of the padded buffer that mirror onto upsampled row u (besides u+pad itself)
-__device__ __forceinline__ int fold_candidates(int u, int n, int pad, int out[3]) {
-  int cnt = 0;
-  out[cnt++] = u + pad;
-  if (u >= 1 && u <= pad) out[cnt++] = pad - u;                                   // top / left halo
-  if (u <= n - 2 && u >= n - 1 - pad) out[cnt++] = 2 * (n - 1) - u + pad;         // bottom / right halo
-  return cnt;
+__device__ __forceinline__ void fold_candidates(int u, int n, int pad, int out[3]) {
+  out[0] = u + pad;
+  out[1] = (u >= 1 && u <= pad) ? pad - u : -1;                                   // top / left halo
+  out[2] = (u <= n - 2 && u >= n - 1 - pad) ? 2 * (n - 1) - u + pad : -1;         // bottom / right halo
 }
 
 // backward pass 1 (see header).  One thread per source pixel x 8 channels; block = 256 threads laid out
@@ -194,44 +192,52 @@ __global__ void __launch_bounds__(256)
   const int c8 = threadIdx.x % C8, lane_p = threadIdx.x / C8, ppb = 256 / C8;
   const int Hu = H * up, Wu = W * up, Hd = Hu + 2 * pad, Wd = Wu + 2 * pad;
   const float a = prelu_a != nullptr ? *prelu_a : 0.f;
-  const int64_t pixels = (int64_t)B * H * W;
+  const uint32_t pixels = (uint32_t)B * H * W;   // < 2^31, checked by the caller
   float s1[8], s2[8];
   float sa = 0.f;
 #pragma unroll
   for (int k = 0; k < 8; ++k) s1[k] = s2[k] = 0.f;
-  for (int64_t p = (int64_t)blockIdx.x * ppb + lane_p; p < pixels; p += (int64_t)gridDim.x * ppb) {
-    const int x = (int)(p % W);
-    const int y = (int)((p / W) % H);
-    const int n = (int)(p / ((int64_t)W * H));
+  for (uint32_t p = blockIdx.x * ppb + lane_p; p < pixels; p += gridDim.x * ppb) {
+    const int x = (int)(p % (uint32_t)W);
+    const uint32_t pq = p / (uint32_t)W;
+    const int y = (int)(pq % (uint32_t)H);
+    const int n = (int)(pq / (uint32_t)H);
     float g[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) g[k] = 0.f;
     if (dpad != nullptr) {
+      // every padded position that mirrors / upsamples onto this source pixel; the interior case (one or
+      // up*up reads) is the common one, halo candidates are -1 away from the borders
       for (int uy = y * up; uy < y * up + up; ++uy) {
         int rows[3];
-        const int nr = fold_candidates(uy, Hu, pad, rows);
+        fold_candidates(uy, Hu, pad, rows);
         for (int ux = x * up; ux < x * up + up; ++ux) {
           int cols[3];
-          const int nc = fold_candidates(ux, Wu, pad, cols);
-          for (int a_ = 0; a_ < nr; ++a_)
-            for (int b_ = 0; b_ < nc; ++b_) {
+          fold_candidates(ux, Wu, pad, cols);
+#pragma unroll
+          for (int a_ = 0; a_ < 3; ++a_) {
+            if (rows[a_] < 0) continue;
+#pragma unroll
+            for (int b_ = 0; b_ < 3; ++b_) {
+              if (cols[b_] < 0) continue;
               float t[8];
               ld8(dpad + (((int64_t)n * Hd + rows[a_]) * Wd + cols[b_]) * C + c8 * 8, t);
 #pragma unroll
               for (int k = 0; k < 8; ++k) g[k] += t[k];
             }
+          }
         }
       }
     }
     if (g1 != nullptr) {
       float t[8];
-      ld8(g1 + p * C + c8 * 8, t);
+      ld8(g1 + (size_t)p * C + c8 * 8, t);
 #pragma unroll
       for (int k = 0; k < 8; ++k) g[k] += t[k];
     }
     if (g2 != nullptr) {
       float t[8];
-      ld8(g2 + p * C + c8 * 8, t);
+      ld8(g2 + (size_t)p * C + c8 * 8, t);
 #pragma unroll
       for (int k = 0; k < 8; ++k) g[k] += t[k];
     }
@@ -243,7 +249,7 @@ __global__ void __launch_bounds__(256)
       }
     }
     float rv[8], sk[8];
-    ld8(r + p * C + c8 * 8, rv);
+    ld8(r + (size_t)p * C + c8 * 8, rv);
     if (skip != nullptr)
       ld8(skip + (((int64_t)n * (H + 2 * skip_pad) + y + skip_pad) * (W + 2 * skip_pad) + x + skip_pad) * C + c8 * 8, sk);
     float o[8];
@@ -259,7 +265,7 @@ __global__ void __launch_bounds__(256)
       s1[k] += dq;
       if (sb != nullptr) s2[k] += dq * (rv[k] - sb[2 * C + c]) * sb[3 * C + c];
     }
-    st8(dz + p * C + c8 * 8, o);
+    st8(dz + (size_t)p * C + c8 * 8, o);
   }
   if (red != nullptr) {
     __shared__ float sh[2][8][256];
@@ -301,8 +307,8 @@ __global__ void __launch_bounds__(256)
   }
   for (int64_t p = (int64_t)blockIdx.x * ppb + lane_p; p < pixels; p += (int64_t)gridDim.x * ppb) {
     float d[8], rv[8];
-    ld8(dz + p * C + c8 * 8, d);
-    ld8(r + p * C + c8 * 8, rv);
+    ld8(dz + (size_t)p * C + c8 * 8, d);
+    ld8(r + (size_t)p * C + c8 * 8, rv);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       const float xh = (rv[k] - mean[k]) * istd[k];
@@ -310,7 +316,7 @@ __global__ void __launch_bounds__(256)
       d[k] = v;
       sd[k] += v;
     }
-    st8(dr + p * C + c8 * 8, d);
+    st8(dr + (size_t)p * C + c8 * 8, d);
   }
   if (dbias != nullptr) {
     __shared__ float sh[8][256];
@@ -482,17 +488,17 @@ __global__ void __launch_bounds__(256)
 #pragma unroll
     for (int k = 0; k < 8; ++k) g[k] = 0.f;
     if (ga != nullptr) {
-      ld8(ga + p * C + c8 * 8, t);
+      ld8(ga + (size_t)p * C + c8 * 8, t);
 #pragma unroll
       for (int k = 0; k < 8; ++k) g[k] += t[k];
     }
     if (gb != nullptr) {
-      ld8(gb + p * C + c8 * 8, t);
+      ld8(gb + (size_t)p * C + c8 * 8, t);
 #pragma unroll
       for (int k = 0; k < 8; ++k) g[k] += t[k];
     }
     if (act == P2P_ACT_LRELU) {
-      ld8(out + p * C + c8 * 8, o);
+      ld8(out + (size_t)p * C + c8 * 8, o);
 #pragma unroll
       for (int k = 0; k < 8; ++k) g[k] *= (o[k] > 0.f ? 1.f : 0.2f);
     }
@@ -501,7 +507,7 @@ __global__ void __launch_bounds__(256)
       if (c8 * 8 + k >= c_real) g[k] = 0.f;
       sd[k] += round_as(g[k], dz);
     }
-    st8(dz + p * C + c8 * 8, g);
+    st8(dz + (size_t)p * C + c8 * 8, g);
   }
   if (dbias != nullptr) {
     __shared__ float sh[8][256];
@@ -553,6 +559,12 @@ static inline int ew_grid(int64_t total, int block = 256) {
   const int64_t cap = (int64_t)kSMs * 16;
   return (int)(g < 1 ? 1 : (g > cap ? cap : g));
 }
+// kernels that end in per-channel atomics: 4 resident blocks per SM, so each address sees <= 592 adds
+static inline int red_ew_grid(int64_t pixels, int ppb) {
+  int64_t g = (pixels + ppb - 1) / ppb;
+  const int64_t cap = (int64_t)kSMs * 4;
+  return (int)(g < 1 ? 1 : (g > cap ? cap : g));
+}
 
 }  // namespace p2p
 
@@ -572,7 +584,7 @@ int p2p_channel_stats(const void* r, double* stats, int64_t pixels, int C, int d
   P2P_REQUIRE(r && stats && pixels > 0, "null pointer or empty map");
   P2P_REQUIRE(C % 16 == 0 && C <= 512, "C must be a multiple of 16, <= 512");
   const int ppb = 256 / (C / 8);
-  P2P_DISPATCH(dtype, channel_stats_kernel<T><<<ew_grid(pixels, ppb), 256, 0, as_stream(stream)>>>((const T*)r, stats,
+  P2P_DISPATCH(dtype, channel_stats_kernel<T><<<red_ew_grid(pixels, ppb), 256, 0, as_stream(stream)>>>((const T*)r, stats,
                                                                                                 pixels, C););
   P2P_LAUNCH_CHECK();
 }
@@ -602,6 +614,7 @@ int p2p_bn_act_store(const void* r, const float* sb, const void* skip, int skip_
     P2P_LAUNCH_CHECK();
   }
   const int64_t total = (int64_t)B * (H * up + 2 * pad) * (W * up + 2 * pad) * (C / 8);
+  P2P_REQUIRE(total < (1LL << 31), "tensor too large");
   P2P_DISPATCH(dtype, bn_act_store_kernel<T><<<ew_grid(total), 256, 0, as_stream(stream)>>>(
                           (const T*)r, sb, (const T*)skip, skip_pad, prelu_a, (T*)dst, B, H, W, C, act, up, pad););
   P2P_LAUNCH_CHECK();
@@ -617,7 +630,8 @@ int p2p_bn_act_bwd_reduce(const void* dpad, const void* g1, const void* g2, cons
   P2P_REQUIRE(act != P2P_ACT_PRELU || prelu_a, "PReLU needs its slope");
   const int ppb = 256 / (C / 8);
   const int64_t pixels = (int64_t)B * H * W;
-  P2P_DISPATCH(dtype, bn_act_bwd_reduce_kernel<T><<<ew_grid(pixels, ppb), 256, 0, as_stream(stream)>>>(
+  P2P_REQUIRE((int64_t)B * (H * up + 2 * pad) * (W * up + 2 * pad) * (C / 8) < (1LL << 31), "tensor too large");
+  P2P_DISPATCH(dtype, bn_act_bwd_reduce_kernel<T><<<red_ew_grid(pixels, ppb), 256, 0, as_stream(stream)>>>(
                           (const T*)dpad, (const T*)g1, (const T*)g2, g_nchw, (const T*)r, sb, (const T*)skip, skip_pad,
                           prelu_a, (T*)dz, red, dprelu, B, H, W, C, c_real, act, up, pad););
   P2P_LAUNCH_CHECK();
@@ -628,7 +642,7 @@ int p2p_bn_bwd_apply(const void* dz, const void* r, const float* sb, const doubl
   P2P_REQUIRE(dz && r && sb && red && dr, "null pointer");
   P2P_REQUIRE(C % 16 == 0 && C <= 512, "C must be a multiple of 16, <= 512");
   const int ppb = 256 / (C / 8);
-  P2P_DISPATCH(dtype, bn_bwd_apply_kernel<T><<<ew_grid(pixels, ppb), 256, 0, as_stream(stream)>>>(
+  P2P_DISPATCH(dtype, bn_bwd_apply_kernel<T><<<red_ew_grid(pixels, ppb), 256, 0, as_stream(stream)>>>(
                           (const T*)dz, (const T*)r, sb, red, (T*)dr, dbias, pixels, C, c_real););
   if (dgamma != nullptr && dbeta != nullptr) {
     bn_param_grad_kernel<<<cdiv(C, 128), 128, 0, as_stream(stream)>>>(red, dgamma, dbeta, C, c_real);
@@ -689,7 +703,7 @@ int p2p_act_bwd(const void* out, const void* g_a, const void* g_b, void* dz, flo
   P2P_REQUIRE(act == P2P_ACT_NONE || (act == P2P_ACT_LRELU && out), "LeakyReLU gradient needs the forward output");
   P2P_REQUIRE(C % 16 == 0 && C <= 512, "C must be a multiple of 16, <= 512");
   const int ppb = 256 / (C / 8);
-  P2P_DISPATCH(dtype, act_bwd_kernel<T><<<ew_grid(pixels, ppb), 256, 0, as_stream(stream)>>>(
+  P2P_DISPATCH(dtype, act_bwd_kernel<T><<<red_ew_grid(pixels, ppb), 256, 0, as_stream(stream)>>>(
                           (const T*)out, (const T*)g_a, (const T*)g_b, (T*)dz, dbias, pixels, C, c_real, act););
   P2P_LAUNCH_CHECK();
 }
