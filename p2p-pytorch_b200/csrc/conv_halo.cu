@@ -7,9 +7,10 @@
 // chunk, and every tap is just a different UMMA descriptor into that tile:
 //     row(m, tap) = (m/8 + dh)*HW + (m%8 + dw)          start address = base + row*pitch, SBO = HW*pitch
 // which works because tcgen05.mma applies the shared-memory swizzle to absolute address bits (probed on
-// hardware: tools/probe/umma_shift_probe.cu -- row-shifted starts and SBO != 8 rows give exact results).
-// Only the weights still stream per (tap, chunk), and each weight tile feeds two accumulator tiles, so the
-// L2->SM traffic per 128 output pixels drops from 576 KB to ~190 KB for the 3x3 128->128 layer.
+// hardware: tools/probe/umma_shift_probe*.cu -- row-shifted starts and SBO != 8 rows give exact results for
+// 32/64/128-byte rows).  Weights either stream through a ring, one [BLOCK_N x CIN_BLK] tile per (tap, chunk)
+// feeding both accumulator tiles, or -- when the whole filter bank of the layer fits in ~100 KB (the 9x9
+// layers, deconv2) -- are loaded once per CTA and stay resident, so the steady state moves only halos.
 //
 // Persistent kernel, one CTA per SM, 7 warps:  warp 0 = halo (A) TMA producer, warp 6 = weight (B) TMA
 // producer, warp 1 = MMA issuer, warps 2-5 = epilogue.  TMEM holds two accumulator sets (2 tiles x BLOCK_N
@@ -33,14 +34,11 @@ struct HaloParams {
   int blocks_w, blocks_h, n_img;        // 32x8 pixel blocks per image
   int min_dh, min_dw, HW, HH;           // halo geometry (halo is HH x HW pixels)
   int a_bytes;                          // bytes of one halo chunk buffer (1024-aligned)
-  int nb;                               // weight ring depth
-  int Hv, Wv;                           // valid output-position grid
-  int64_t out_sN, out_sH, out_sW;
-  int h_mul, h_off, w_mul, w_off;
-  int co_real, act, Cn;
-  __nv_bfloat16* out;
+  int nb;                               // weight ring depth (streaming) / number of resident tiles
+  int resident;                         // 1: all n_taps * c_chunks weight tiles stay in shared memory
+  EpiOut epi;                           // output addressing, bias handled separately
+  int64_t out_sN;
   const float* bias;
-  double* stats;
   HaloTap taps[kHaloMaxTaps];
 };
 
@@ -58,20 +56,22 @@ __global__ void __launch_bounds__(224, 1)
   uint8_t* sA = smem;
   uint8_t* sB = sA + NA * p.a_bytes;
   uint8_t* stg = sB + p.nb * B_BYTES;
+  float* s_red = reinterpret_cast<float*>(stg + 128 * PITCH);
   __shared__ uint64_t a_full[NA], a_empty[NA], b_full[8], b_empty[8], t_full[2], t_empty[2];
   __shared__ uint32_t tmem_base_s;
-  __shared__ float s_bias[BLOCK_N];
+  __shared__ __align__(16) float s_bias[BLOCK_N];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int blocks_per_img = p.blocks_w * p.blocks_h;
   const int items_per_ntile = blocks_per_img * p.n_img;
   const int n_items = items_per_ntile * p.n_tiles;
+  const int n_ring = p.resident ? 1 : p.nb;
 
   if (threadIdx.x == 0) {
     prefetch_tmap(&map_a);
     prefetch_tmap(&map_b);
     for (int s = 0; s < NA; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); }
-    for (int s = 0; s < p.nb; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
+    for (int s = 0; s < n_ring; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(&t_full[s], 1); mbar_init(&t_empty[s], 4); }
     fence_barrier_init();
   }
@@ -97,18 +97,26 @@ __global__ void __launch_bounds__(224, 1)
       }
     }
   } else if (threadIdx.x == 192) {
-    // ===== weight producer: one tile per (item, chunk, tap) =====
-    int bs = 0;
-    uint32_t bph = 0;
-    for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
-      const int n0 = (it / items_per_ntile) * BLOCK_N;
+    // ===== weight producer =====
+    if (p.resident) {
+      // the whole filter bank once: tile (c, t) lives at sB + (c * n_taps + t) * B_BYTES for the kernel's lifetime
+      mbar_arrive_expect_tx(&b_full[0], (uint32_t)(p.c_chunks * p.n_taps * B_BYTES));
       for (int c = 0; c < p.c_chunks; ++c)
-        for (int t = 0; t < p.n_taps; ++t) {
-          mbar_wait(&b_empty[bs], bph ^ 1);
-          mbar_arrive_expect_tx(&b_full[bs], B_BYTES);
-          tma_load_2d(sB + bs * B_BYTES, &map_b, &b_full[bs], p.taps[t].wk + c * CIN_BLK, n0);
-          if (++bs == p.nb) { bs = 0; bph ^= 1; }
-        }
+        for (int t = 0; t < p.n_taps; ++t)
+          tma_load_2d(sB + (c * p.n_taps + t) * B_BYTES, &map_b, &b_full[0], p.taps[t].wk + c * CIN_BLK, 0);
+    } else {
+      int bs = 0;
+      uint32_t bph = 0;
+      for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+        const int n0 = (it / items_per_ntile) * BLOCK_N;
+        for (int c = 0; c < p.c_chunks; ++c)
+          for (int t = 0; t < p.n_taps; ++t) {
+            mbar_wait(&b_empty[bs], bph ^ 1);
+            mbar_arrive_expect_tx(&b_full[bs], B_BYTES);
+            tma_load_2d(sB + bs * B_BYTES, &map_b, &b_full[bs], p.taps[t].wk + c * CIN_BLK, n0);
+            if (++bs == p.nb) { bs = 0; bph ^= 1; }
+          }
+      }
     }
   } else if (threadIdx.x == 32) {
     // ===== MMA issuer =====
@@ -116,6 +124,7 @@ __global__ void __launch_bounds__(224, 1)
     const uint32_t sbo_field = (uint32_t)((p.HW * RB) >> 4) & 0x3FFF;
     int ab = 0, bs = 0, li = 0;
     uint32_t aph = 0, bph = 0;
+    if (p.resident) mbar_wait(&b_full[0], 0);
     for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++li) {
       const int set = li & 1;
       mbar_wait(&t_empty[set], ((li >> 1) & 1) ^ 1);
@@ -123,23 +132,31 @@ __global__ void __launch_bounds__(224, 1)
       const uint32_t acc = tmem_base + set * 2 * BLOCK_N;
       for (int c = 0; c < p.c_chunks; ++c) {
         mbar_wait(&a_full[ab], aph);
+        tc_fence_after();
         const uint32_t a_base = smem_u32(sA + ab * p.a_bytes);
         for (int t = 0; t < p.n_taps; ++t) {
-          mbar_wait(&b_full[bs], bph);
-          tc_fence_after();
-          const uint32_t b_base = smem_u32(sB + bs * B_BYTES);
+          uint32_t b_base;
+          if (p.resident) {
+            b_base = smem_u32(sB + (c * p.n_taps + t) * B_BYTES);
+          } else {
+            mbar_wait(&b_full[bs], bph);
+            tc_fence_after();
+            b_base = smem_u32(sB + bs * B_BYTES);
+          }
           const uint32_t a_tap = a_base + (uint32_t)p.taps[t].row_off * RB;
 #pragma unroll
-          for (int h = 0; h < 2; ++h) {
+          for (int k = 0; k < CIN_BLK / 16; ++k) {
 #pragma unroll
-            for (int k = 0; k < CIN_BLK / 16; ++k) {
+            for (int h = 0; h < 2; ++h) {
               uint64_t ad = smem_desc_kmajor(a_tap + h * 16 * p.HW * RB + k * 32, RB);
               ad = (ad & ~(uint64_t(0x3FFF) << 32)) | ((uint64_t)sbo_field << 32);   // 8-row groups are HW rows apart
               umma_bf16(acc + h * BLOCK_N, ad, smem_desc_kmajor(b_base + k * 32, RB), idesc, (c | t | k) != 0 ? 1u : 0u);
             }
           }
-          umma_commit(&b_empty[bs]);
-          if (++bs == p.nb) { bs = 0; bph ^= 1; }
+          if (!p.resident) {
+            umma_commit(&b_empty[bs]);
+            if (++bs == p.nb) { bs = 0; bph ^= 1; }
+          }
         }
         umma_commit(&a_empty[ab]);
         if (++ab == NA) { ab = 0; aph ^= 1; }
@@ -149,10 +166,11 @@ __global__ void __launch_bounds__(224, 1)
   } else if (warp >= 2 && warp <= 5) {
     // ===== epilogue =====
     const int q = warp & 3;
-    const int row = q * 32 + lane;          // accumulator row = pixel (row/8, row%8) of the 16x8 tile
     const int et = threadIdx.x - 64;        // 0..127
     int li = 0;
     int cur_n0 = -1;
+    EpiOut e = p.epi;
+    e.tw_log2 = 3;
     for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++li) {
       const int set = li & 1;
       const int n0 = (it / items_per_ntile) * BLOCK_N;
@@ -162,77 +180,20 @@ __global__ void __launch_bounds__(224, 1)
       if (n0 != cur_n0) {
         named_bar_sync(1, 128);
         for (int i = et; i < BLOCK_N; i += 128)
-          s_bias[i] = (p.bias != nullptr && n0 + i < p.co_real) ? p.bias[n0 + i] : 0.f;
+          s_bias[i] = (p.bias != nullptr && n0 + i < e.co_real) ? p.bias[n0 + i] : 0.f;
         named_bar_sync(1, 128);
         cur_n0 = n0;
       }
+      e.n0 = n0;
+      e.out = p.epi.out + (int64_t)img * p.out_sN;
+      e.ox0 = ox0;
       mbar_wait(&t_full[set], (li >> 1) & 1);
       tc_fence_after();
 #pragma unroll 1
       for (int h = 0; h < 2; ++h) {
-        const int ty = h * 16 + (row >> 3), tx = row & 7;
-        const bool valid = (oy0 + ty) < p.Hv && (ox0 + tx) < p.Wv;
-        constexpr int CH = BLOCK_N >= 32 ? 32 : 16;
-#pragma unroll 1
-        for (int c0 = 0; c0 < BLOCK_N; c0 += CH) {
-          uint32_t v[32];
-          const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(set * 2 * BLOCK_N + h * BLOCK_N + c0);
-          if (CH == 32) tmem_ld32(taddr, v); else tmem_ld16(taddr, v);
-          tmem_ld_wait();
-          uint32_t pk[CH / 2];
-#pragma unroll
-          for (int j = 0; j < CH; j += 2) {
-            float f0 = __uint_as_float(v[j]) + s_bias[c0 + j];
-            float f1 = __uint_as_float(v[j + 1]) + s_bias[c0 + j + 1];
-            if (p.act == P2P_ACT_LRELU) {
-              f0 = f0 > 0.f ? f0 : 0.2f * f0;
-              f1 = f1 > 0.f ? f1 : 0.2f * f1;
-            }
-            if (!valid || n0 + c0 + j >= p.co_real) f0 = 0.f;
-            if (!valid || n0 + c0 + j + 1 >= p.co_real) f1 = 0.f;
-            pk[j / 2] = pack_bf16x2(f0, f1);
-          }
-          uint4* dst = reinterpret_cast<uint4*>(stg + row * PITCH + c0 * 2);
-#pragma unroll
-          for (int j = 0; j < CH / 8; ++j) dst[j] = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
-        }
-        if (h == 1) {
-          // both tiles of this accumulator set are in registers / staging: hand the set back to the MMA warp
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&t_empty[set]);
-        }
-        named_bar_sync(1, 128);
-        if (p.stats != nullptr) {
-          for (int c = et; c < BLOCK_N; c += 128) {
-            if (n0 + c < p.co_real) {
-              float s = 0.f, ss = 0.f;
-#pragma unroll 8
-              for (int rr = 0; rr < 128; ++rr) {
-                const float f = __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(stg + rr * PITCH + c * 2));
-                s += f;
-                ss = fmaf(f, f, ss);
-              }
-              atomicAdd(p.stats + n0 + c, (double)s);
-              atomicAdd(p.stats + p.Cn + n0 + c, (double)ss);
-            }
-          }
-        }
-        constexpr int LPR = BLOCK_N / 8;   // lanes per pixel row (16 B each)
-        constexpr int RPI = 128 / LPR;
-        const int sub = et % LPR, r_in = et / LPR;
-#pragma unroll 1
-        for (int r0 = 0; r0 < 128; r0 += RPI) {
-          const int rr = r0 + r_in;
-          const int yy = oy0 + h * 16 + (rr >> 3), xx = ox0 + (rr & 7);
-          if (yy < p.Hv && xx < p.Wv) {
-            const uint4 val = *reinterpret_cast<const uint4*>(stg + rr * PITCH + sub * 16);
-            __nv_bfloat16* o = p.out + (int64_t)img * p.out_sN + (int64_t)(yy * p.h_mul + p.h_off) * p.out_sH +
-                               (int64_t)(xx * p.w_mul + p.w_off) * p.out_sW + n0 + sub * 8;
-            *reinterpret_cast<uint4*>(o) = val;
-          }
-        }
-        named_bar_sync(1, 128);   // staging is reused by the next tile
+        e.oy0 = oy0 + h * 16;
+        epilogue_tile<BLOCK_N>(tmem_base + (uint32_t)(set * 2 * BLOCK_N + h * BLOCK_N), q, lane, et, stg, s_bias, s_red, e,
+                               h == 1 ? &t_empty[set] : nullptr);
       }
     }
   }
@@ -267,12 +228,12 @@ static int launch_halo_n(int block_n, const CUtensorMap& ma, const CUtensorMap& 
   }
 }
 
-// A stride-1 implicit-GEMM problem.  taps: (dh, dw, wk) triples.  Returns -2 when the shape does not fit
-// (the caller then uses the per-tap kernel of conv_tc.cu).
+// A stride-1 implicit-GEMM problem.  taps: (dh, dw, wk) triples.  Returns -2 when the shape does not fit or
+// the per-tap kernel of conv_tc.cu is the better choice (the caller then uses that one).
 int run_halo_problem(const void* a_src, int N, int Hs, int Ws, int Ck, const void* b_mat, int Cn, int64_t ktot,
                      const int* dh, const int* dw, const int* wk, int n_taps, int Hv, int Wv, __nv_bfloat16* out,
                      int64_t out_sN, int64_t out_sH, int64_t out_sW, int h_mul, int h_off, int w_mul, int w_off,
-                     int co_real, int act, const float* bias, double* stats, cudaStream_t st) {
+                     int co_real, int act, const float* bias, double* stats, bool force, cudaStream_t st) {
   if (n_taps > kHaloMaxTaps) return -2;
   const int cin_blk = Ck >= 64 ? 64 : Ck;
   const int block_n = Cn >= 128 ? 128 : Cn;
@@ -289,14 +250,31 @@ int run_halo_problem(const void* a_src, int N, int Hs, int Ws, int Ck, const voi
   p.min_dh = mn_h;
   p.min_dw = mn_w;
   p.a_bytes = ((p.HH * p.HW * rb + 1023) / 1024) * 1024;
+  p.c_chunks = Ck / cin_blk;
+  p.n_tiles = Cn / block_n;
   const int b_bytes = block_n * rb;
-  const int stg_bytes = 128 * (block_n * 2 + 16);
-  int nb = (48 * 1024) / b_bytes;
-  nb = nb > 8 ? 8 : nb;
-  int smem = 2 * p.a_bytes + nb * b_bytes + stg_bytes + 1024;
-  while (smem > 225 * 1024 && nb > 2) { --nb; smem -= b_bytes; }
-  if (smem > 225 * 1024) return -2;
+  const int stg_bytes = 128 * (block_n * 2 + 16) + 8192;   // staging + statistics scratch
+  const int budget = 225 * 1024 - 2 * p.a_bytes - stg_bytes - 1024;
+  const int bank_tiles = n_taps * p.c_chunks;
+  p.resident = (p.n_tiles == 1 && bank_tiles * b_bytes <= budget && bank_tiles * b_bytes <= 112 * 1024) ? 1 : 0;
+  if (!force) {
+    // Measured on B200 (tools/bench_convs.py): with streamed weights this kernel beats the per-tap kernel only
+    // where the output tile is narrow (Cn <= 64); with resident weights it always does.
+    const int64_t blocks = (int64_t)((Wv + 7) / 8) * ((Hv + 31) / 32) * N;
+    if (!p.resident && Cn > 64) return -2;
+    if (blocks * 256 > 2 * (int64_t)N * Hv * Wv) return -2;    // small maps: too many padded pixels per 32x8 block
+  }
+  int nb;
+  if (p.resident) {
+    nb = bank_tiles;
+  } else {
+    nb = budget / b_bytes;
+    nb = nb > 8 ? 8 : nb;
+    if (nb < 2) return -2;
+  }
   p.nb = nb;
+  const int smem = 2 * p.a_bytes + nb * b_bytes + stg_bytes + 1024;
+  if (smem > 226 * 1024) return -2;
   p.n_taps = n_taps;
   for (int t = 0; t < n_taps; ++t) {
     const int ro = (dh[t] - mn_h) * p.HW + (dw[t] - mn_w);
@@ -304,16 +282,16 @@ int run_halo_problem(const void* a_src, int N, int Hs, int Ws, int Ck, const voi
     p.taps[t].row_off = (int16_t)ro;
     p.taps[t].wk = wk[t];
   }
-  p.c_chunks = Ck / cin_blk;
-  p.n_tiles = Cn / block_n;
   p.blocks_w = (Wv + 7) / 8;
   p.blocks_h = (Hv + 31) / 32;
   p.n_img = N;
-  p.Hv = Hv; p.Wv = Wv;
-  p.out_sN = out_sN; p.out_sH = out_sH; p.out_sW = out_sW;
-  p.h_mul = h_mul; p.h_off = h_off; p.w_mul = w_mul; p.w_off = w_off;
-  p.co_real = co_real; p.act = act; p.Cn = Cn;
-  p.out = out; p.bias = bias; p.stats = stats;
+  p.out_sN = out_sN;
+  p.bias = bias;
+  p.epi.out = out;
+  p.epi.out_sH = out_sH; p.epi.out_sW = out_sW;
+  p.epi.h_mul = h_mul; p.epi.h_off = h_off; p.epi.w_mul = w_mul; p.epi.w_off = w_off;
+  p.epi.Hv = Hv; p.epi.Wv = Wv;
+  p.epi.co_real = co_real; p.epi.Cn = Cn; p.epi.act = act; p.epi.stats = stats;
 
   CUtensorMap ma, mb;
   {

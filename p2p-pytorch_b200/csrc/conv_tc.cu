@@ -51,7 +51,7 @@ struct TcCfg {
   static constexpr int PITCH = BLOCK_N * 2 + 16;  // epilogue staging row pitch (bytes), bank-conflict free
   static constexpr int SMEM = STAGES * STAGE_BYTES + 1024;
   static constexpr int TMEM_COLS = BLOCK_N < 32 ? 32 : BLOCK_N;
-  static_assert(128 * PITCH <= STAGES * STAGE_BYTES, "epilogue staging must fit in the pipeline buffers");
+  static_assert(128 * PITCH + 8192 <= STAGES * STAGE_BYTES, "epilogue staging must fit in the pipeline buffers");
 };
 
 template <int BLOCK_N, int CIN_BLK>
@@ -65,7 +65,7 @@ __global__ void __launch_bounds__(192)
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   __shared__ uint64_t full_bar[STAGES], empty_bar[STAGES], tmem_full_bar;
   __shared__ uint32_t tmem_base_s;
-  __shared__ float s_bias[BLOCK_N];
+  __shared__ __align__(16) float s_bias[BLOCK_N];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tiles_per_img = p.tiles_w * p.tiles_h;
@@ -132,70 +132,20 @@ __global__ void __launch_bounds__(192)
     umma_commit(&tmem_full_bar);
   } else if (warp >= 2) {
     // ===== epilogue =====
-    const int q = warp & 3;  // TMEM lane quarter this warp may access
-    const int row = q * 32 + lane;
-    const int ty = row >> p.tw_log2, tx = row & (p.tw - 1);
-    const bool valid = (oy0 + ty) < p.Hv && (ox0 + tx) < p.Wv;
     mbar_wait(&tmem_full_bar, 0);
     tc_fence_after();
-    uint8_t* stg = smem;  // pipeline buffers are idle now: every MMA that read them has completed
-    constexpr int CH = BLOCK_N >= 32 ? 32 : 16;
-#pragma unroll 1
-    for (int c0 = 0; c0 < BLOCK_N; c0 += CH) {
-      uint32_t v[32];
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0;
-      if (CH == 32) tmem_ld32(taddr, v); else tmem_ld16(taddr, v);
-      tmem_ld_wait();
-      uint32_t pk[CH / 2];
-#pragma unroll
-      for (int j = 0; j < CH; j += 2) {
-        float f0 = __uint_as_float(v[j]) + s_bias[c0 + j];
-        float f1 = __uint_as_float(v[j + 1]) + s_bias[c0 + j + 1];
-        if (p.act == P2P_ACT_LRELU) {
-          f0 = f0 > 0.f ? f0 : 0.2f * f0;
-          f1 = f1 > 0.f ? f1 : 0.2f * f1;
-        }
-        if (!valid || n0 + c0 + j >= p.co_real) f0 = 0.f;
-        if (!valid || n0 + c0 + j + 1 >= p.co_real) f1 = 0.f;
-        pk[j / 2] = pack_bf16x2(f0, f1);
-      }
-      uint4* dst = reinterpret_cast<uint4*>(stg + row * Cfg::PITCH + c0 * 2);
-#pragma unroll
-      for (int j = 0; j < CH / 8; ++j) dst[j] = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
-    }
-    named_bar_sync(1, 128);
-    const int et = threadIdx.x - 64;  // 0..127
-    if (p.stats != nullptr) {
-      // BatchNorm statistics of the tile as stored (bf16-rounded), one channel per thread
-      for (int c = et; c < BLOCK_N; c += 128) {
-        if (n0 + c < p.co_real) {
-          float s = 0.f, ss = 0.f;
-#pragma unroll 8
-          for (int r = 0; r < 128; ++r) {
-            const float f = __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(stg + r * Cfg::PITCH + c * 2));
-            s += f;
-            ss = fmaf(f, f, ss);
-          }
-          atomicAdd(p.stats + n0 + c, (double)s);
-          atomicAdd(p.stats + p.Cn + n0 + c, (double)ss);
-        }
-      }
-    }
-    // coalesced stores: LPR lanes cover one pixel's BLOCK_N channels (16 B each)
-    constexpr int LPR = BLOCK_N / 8;
-    constexpr int RPI = 128 / LPR;  // rows per iteration over the 128 epilogue threads
-    const int sub = et % LPR, r_in = et / LPR;
-#pragma unroll 1
-    for (int r0 = 0; r0 < 128; r0 += RPI) {
-      const int r = r0 + r_in;
-      const int yy = oy0 + (r >> p.tw_log2), xx = ox0 + (r & (p.tw - 1));
-      if (yy < p.Hv && xx < p.Wv) {
-        const uint4 val = *reinterpret_cast<const uint4*>(stg + r * Cfg::PITCH + sub * 16);
-        __nv_bfloat16* o = p.out + (int64_t)n_img * p.out_sN + (int64_t)(yy * p.h_mul + p.h_off) * p.out_sH +
-                           (int64_t)(xx * p.w_mul + p.w_off) * p.out_sW + n0 + sub * 8;
-        *reinterpret_cast<uint4*>(o) = val;
-      }
-    }
+    // pipeline buffers are idle now (every MMA that read them has completed): reuse them as staging
+    uint8_t* stg = smem;
+    float* s_red = reinterpret_cast<float*>(smem + 128 * Cfg::PITCH);
+    EpiOut e;
+    e.out = p.out + (int64_t)n_img * p.out_sN;
+    e.out_sH = p.out_sH; e.out_sW = p.out_sW;
+    e.h_mul = p.h_mul; e.h_off = p.h_off; e.w_mul = p.w_mul; e.w_off = p.w_off;
+    e.Hv = p.Hv; e.Wv = p.Wv;
+    e.oy0 = oy0; e.ox0 = ox0; e.tw_log2 = p.tw_log2;
+    e.n0 = n0; e.co_real = p.co_real; e.Cn = p.Cn; e.act = p.act;
+    e.stats = p.stats;
+    epilogue_tile<BLOCK_N>(tmem_base, warp & 3, lane, threadIdx.x - 64, stg, s_bias, s_red, e, nullptr);
   }
   tc_fence_before();
   __syncthreads();
@@ -257,9 +207,10 @@ static int launch_n(int block_n, const CUtensorMap& ma, const CUtensorMap& mb, c
 int run_halo_problem(const void* a_src, int N, int Hs, int Ws, int Ck, const void* b_mat, int Cn, int64_t ktot,
                      const int* dh, const int* dw, const int* wk, int n_taps, int Hv, int Wv, __nv_bfloat16* out,
                      int64_t out_sN, int64_t out_sH, int64_t out_sW, int h_mul, int h_off, int w_mul, int w_off,
-                     int co_real, int act, const float* bias, double* stats, cudaStream_t st);
+                     int co_real, int act, const float* bias, double* stats, bool force, cudaStream_t st);
 
-static bool g_use_halo = true;   // P2P_NO_HALO=1 forces the per-tap kernel (A/B comparisons)
+static bool g_use_halo = true;    // P2P_NO_HALO=1 forces the per-tap kernel, P2P_FORCE_HALO=1 the halo kernel
+static bool g_force_halo = false;  // (A/B comparisons; by default run_halo_problem picks per shape)
 
 static int run_problem(const void* a_src, int N, int Hs, int Ws, int Ck, const void* b_mat, int Cn, int64_t ktot,
                        TcConvParams& p, cudaStream_t st) {
@@ -267,6 +218,8 @@ static int run_problem(const void* a_src, int N, int Hs, int Ws, int Ck, const v
   if (!env_checked) {
     const char* e = getenv("P2P_NO_HALO");
     g_use_halo = !(e != nullptr && e[0] == '1');
+    const char* f = getenv("P2P_FORCE_HALO");
+    g_force_halo = f != nullptr && f[0] == '1';
     env_checked = true;
   }
   if (p.in_mul == 1 && g_use_halo) {
@@ -275,7 +228,7 @@ static int run_problem(const void* a_src, int N, int Hs, int Ws, int Ck, const v
     for (int t = 0; t < p.n_taps; ++t) { dh[t] = p.taps[t].dh; dw[t] = p.taps[t].dw; wk[t] = p.taps[t].wk; }
     const int rc = run_halo_problem(a_src, N, Hs, Ws, Ck, b_mat, Cn, ktot, dh, dw, wk, p.n_taps, p.Hv, p.Wv, p.out,
                                     p.out_sN, p.out_sH, p.out_sW, p.h_mul, p.h_off, p.w_mul, p.w_off, p.co_real, p.act,
-                                    p.bias, p.stats, st);
+                                    p.bias, p.stats, g_force_halo, st);
     if (rc != -2) return rc;
   }
   const int cin_blk = Ck >= 64 ? 64 : Ck;

@@ -206,3 +206,133 @@ __host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N, int a_mn_ma
 
 }  // namespace tc
 }  // namespace p2p
+
+// ---------------------------------------------------------------------------------------------------
+// Shared epilogue of the convolution kernels: one 128 x BLOCK_N fp32 accumulator tile in TMEM ->
+// (+bias, LeakyReLU) -> bf16 staging in shared memory -> per-channel sum / sum of squares (BatchNorm
+// statistics of the tile as stored) -> coalesced 16-byte global stores.  Called by the 4 epilogue warps
+// (128 threads, `et` = 0..127); named barrier 1 is used between the phases.
+// ---------------------------------------------------------------------------------------------------
+namespace p2p {
+namespace tc {
+
+struct EpiOut {
+  __nv_bfloat16* out;               // already offset to the image (n * out_sN)
+  int64_t out_sH, out_sW;
+  int h_mul, h_off, w_mul, w_off;
+  int Hv, Wv;                       // valid output-position grid
+  int oy0, ox0, tw_log2;            // tile origin; row r of the tile is pixel (oy0 + (r >> tw_log2), ox0 + (r & (tw-1)))
+  int n0, co_real, Cn, act;
+  double* stats;
+};
+
+template <int BLOCK_N>
+__device__ __forceinline__ void epilogue_tile(uint32_t tmem_tile, int q, int lane, int et, uint8_t* stg,
+                                              const float* s_bias, float* s_red, const EpiOut& e,
+                                              uint64_t* release_bar) {
+  constexpr int PITCH = BLOCK_N * 2 + 16;
+  constexpr int CH = BLOCK_N >= 32 ? 32 : 16;
+  const int row = q * 32 + lane;
+  const int tw_mask = (1 << e.tw_log2) - 1;
+  const bool valid = (e.oy0 + (row >> e.tw_log2)) < e.Hv && (e.ox0 + (row & tw_mask)) < e.Wv;
+  const bool full_n = e.n0 + BLOCK_N <= e.co_real;
+  const bool lrelu = e.act == P2P_ACT_LRELU;
+  // ---- phase 1: TMEM -> registers -> bf16 -> staging ---------------------------------------------
+#pragma unroll 1
+  for (int c0 = 0; c0 < BLOCK_N; c0 += CH) {
+    uint32_t v[32];
+    const uint32_t taddr = tmem_tile + ((uint32_t)(q * 32) << 16) + (uint32_t)c0;
+    if (CH == 32) tmem_ld32(taddr, v); else tmem_ld16(taddr, v);
+    tmem_ld_wait();
+    uint32_t pk[CH / 2];
+#pragma unroll
+    for (int j = 0; j < CH; j += 4) {
+      const float4 b4 = *reinterpret_cast<const float4*>(s_bias + c0 + j);
+      float f0 = __uint_as_float(v[j]) + b4.x, f1 = __uint_as_float(v[j + 1]) + b4.y;
+      float f2 = __uint_as_float(v[j + 2]) + b4.z, f3 = __uint_as_float(v[j + 3]) + b4.w;
+      if (lrelu) {
+        f0 = fmaxf(f0, 0.2f * f0); f1 = fmaxf(f1, 0.2f * f1);
+        f2 = fmaxf(f2, 0.2f * f2); f3 = fmaxf(f3, 0.2f * f3);
+      }
+      pk[j / 2] = pack_bf16x2(f0, f1);
+      pk[j / 2 + 1] = pack_bf16x2(f2, f3);
+    }
+    if (!full_n) {      // channel padding: stored as exact zeros
+#pragma unroll
+      for (int j = 0; j < CH; j += 2) {
+        const int c = e.n0 + c0 + j;
+        if (c >= e.co_real) pk[j / 2] = 0u;
+        else if (c + 1 >= e.co_real) pk[j / 2] &= 0x0000ffffu;
+      }
+    }
+    if (!valid) {
+#pragma unroll
+      for (int j = 0; j < CH / 2; ++j) pk[j] = 0u;
+    }
+    uint4* dst = reinterpret_cast<uint4*>(stg + row * PITCH + c0 * 2);
+#pragma unroll
+    for (int j = 0; j < CH / 8; ++j) dst[j] = make_uint4(pk[4 * j], pk[4 * j + 1], pk[4 * j + 2], pk[4 * j + 3]);
+  }
+  if (release_bar != nullptr) {   // the accumulator is in shared memory now: give the TMEM tile back
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(release_bar);
+  }
+  named_bar_sync(1, 128);
+  // ---- phase 2: BatchNorm statistics, 8 channels x 16 rows per thread, then 8-way combine ------------
+  if (e.stats != nullptr) {
+    constexpr int G = BLOCK_N / 8;            // channel groups of 8
+    constexpr int RG = 128 / G;               // row groups (threads per channel group)
+    constexpr int RPT = 128 / RG;             // rows per thread
+    const int g = et % G, rg = et / G;
+    float s[8], ss[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s[k] = ss[k] = 0.f;
+#pragma unroll 4
+    for (int r = rg * RPT; r < rg * RPT + RPT; ++r) {
+      const uint4 u = *reinterpret_cast<const uint4*>(stg + r * PITCH + g * 16);
+      const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float a = __uint_as_float(w[k] << 16), b = __uint_as_float(w[k] & 0xffff0000u);
+        s[2 * k] += a; ss[2 * k] = fmaf(a, a, ss[2 * k]);
+        s[2 * k + 1] += b; ss[2 * k + 1] = fmaf(b, b, ss[2 * k + 1]);
+      }
+    }
+    // s_red[2][RG][BLOCK_N]
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      s_red[(0 * RG + rg) * BLOCK_N + g * 8 + k] = s[k];
+      s_red[(1 * RG + rg) * BLOCK_N + g * 8 + k] = ss[k];
+    }
+    named_bar_sync(1, 128);
+    for (int t = et; t < 2 * BLOCK_N; t += 128) {
+      const int which = t / BLOCK_N, c = t % BLOCK_N;
+      if (e.n0 + c < e.co_real) {
+        float a = 0.f;
+#pragma unroll
+        for (int r = 0; r < RG; ++r) a += s_red[(which * RG + r) * BLOCK_N + c];
+        atomicAdd(e.stats + which * e.Cn + e.n0 + c, (double)a);
+      }
+    }
+  }
+  // ---- phase 3: coalesced stores, LPR lanes cover one pixel's BLOCK_N channels (16 B each) ------------
+  constexpr int LPR = BLOCK_N / 8;
+  constexpr int RPI = 128 / LPR;
+  const int sub = et % LPR, r_in = et / LPR;
+#pragma unroll 2
+  for (int r0 = 0; r0 < 128; r0 += RPI) {
+    const int r = r0 + r_in;
+    const int yy = e.oy0 + (r >> e.tw_log2), xx = e.ox0 + (r & tw_mask);
+    if (yy < e.Hv && xx < e.Wv) {
+      const uint4 val = *reinterpret_cast<const uint4*>(stg + r * PITCH + sub * 16);
+      __nv_bfloat16* o = e.out + (int64_t)(yy * e.h_mul + e.h_off) * e.out_sH +
+                         (int64_t)(xx * e.w_mul + e.w_off) * e.out_sW + e.n0 + sub * 8;
+      *reinterpret_cast<uint4*>(o) = val;
+    }
+  }
+  named_bar_sync(1, 128);   // staging (and s_red) may be reused
+}
+
+}  // namespace tc
+}  // namespace p2p
