@@ -24,9 +24,8 @@ using namespace tc;
 constexpr int kHaloMaxTaps = 81;
 
 struct HaloTap {
-  int16_t row_off;  // (dh - min_dh) * HW + (dw - min_dw)
-  int16_t pad_;
-  int32_t wk;       // first K index of this tap in the weight matrix
+  int32_t row_off16;  // ((dh - min_dh) * HW + (dw - min_dw)) * row_bytes / 16: descriptor-address step of the tap
+  int32_t wk;         // first K index of this tap in the weight matrix
 };
 
 struct HaloParams {
@@ -121,7 +120,9 @@ __global__ void __launch_bounds__(224, 1)
   } else if (threadIdx.x == 32) {
     // ===== MMA issuer =====
     constexpr uint32_t idesc = umma_idesc_bf16(128, BLOCK_N, 0, 0);
-    const uint32_t sbo_field = (uint32_t)((p.HW * RB) >> 4) & 0x3FFF;
+    const uint32_t a_hi = desc_hi((uint32_t)(p.HW * RB), RB);     // 8-row groups of the tile are HW halo rows apart
+    const uint32_t b_hi = desc_hi(8 * RB, RB);
+    const uint32_t h_step = (uint32_t)(16 * p.HW * RB) >> 4;      // second tile: 16 halo rows further down
     int ab = 0, bs = 0, li = 0;
     uint32_t aph = 0, bph = 0;
     if (p.resident) mbar_wait(&b_full[0], 0);
@@ -130,32 +131,30 @@ __global__ void __launch_bounds__(224, 1)
       mbar_wait(&t_empty[set], ((li >> 1) & 1) ^ 1);
       tc_fence_after();
       const uint32_t acc = tmem_base + set * 2 * BLOCK_N;
+      uint32_t first = 0;                                         // 0 for the first MMA of each accumulator
       for (int c = 0; c < p.c_chunks; ++c) {
         mbar_wait(&a_full[ab], aph);
         tc_fence_after();
-        const uint32_t a_base = smem_u32(sA + ab * p.a_bytes);
+        const uint32_t a_lo0 = desc_lo(smem_u32(sA + ab * p.a_bytes), 16);
+        uint32_t b_lo = desc_lo(smem_u32(sB + (p.resident ? c * p.n_taps : 0) * B_BYTES), 16);
         for (int t = 0; t < p.n_taps; ++t) {
-          uint32_t b_base;
-          if (p.resident) {
-            b_base = smem_u32(sB + (c * p.n_taps + t) * B_BYTES);
-          } else {
+          if (!p.resident) {
             mbar_wait(&b_full[bs], bph);
             tc_fence_after();
-            b_base = smem_u32(sB + bs * B_BYTES);
+            b_lo = desc_lo(smem_u32(sB + bs * B_BYTES), 16);
           }
-          const uint32_t a_tap = a_base + (uint32_t)p.taps[t].row_off * RB;
+          const uint32_t a_lo = a_lo0 + (uint32_t)p.taps[t].row_off16;
 #pragma unroll
           for (int k = 0; k < CIN_BLK / 16; ++k) {
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-              uint64_t ad = smem_desc_kmajor(a_tap + h * 16 * p.HW * RB + k * 32, RB);
-              ad = (ad & ~(uint64_t(0x3FFF) << 32)) | ((uint64_t)sbo_field << 32);   // 8-row groups are HW rows apart
-              umma_bf16(acc + h * BLOCK_N, ad, smem_desc_kmajor(b_base + k * 32, RB), idesc, (c | t | k) != 0 ? 1u : 0u);
-            }
+            umma_bf16_split(acc, a_lo + 2 * k, a_hi, b_lo + 2 * k, b_hi, idesc, first | (uint32_t)k);
+            umma_bf16_split(acc + BLOCK_N, a_lo + h_step + 2 * k, a_hi, b_lo + 2 * k, b_hi, idesc, first | (uint32_t)k);
           }
+          first = 1;
           if (!p.resident) {
             umma_commit(&b_empty[bs]);
             if (++bs == p.nb) { bs = 0; bph ^= 1; }
+          } else {
+            b_lo += B_BYTES >> 4;
           }
         }
         umma_commit(&a_empty[ab]);
@@ -278,8 +277,7 @@ int run_halo_problem(const void* a_src, int N, int Hs, int Ws, int Ck, const voi
   p.n_taps = n_taps;
   for (int t = 0; t < n_taps; ++t) {
     const int ro = (dh[t] - mn_h) * p.HW + (dw[t] - mn_w);
-    if (ro > 32767) return -2;
-    p.taps[t].row_off = (int16_t)ro;
+    p.taps[t].row_off16 = ro * rb / 16;
     p.taps[t].wk = wk[t];
   }
   p.blocks_w = (Wv + 7) / 8;

@@ -114,18 +114,17 @@ __global__ void __launch_bounds__(192)
   } else if (threadIdx.x == 32) {
     // ===== MMA issuer =====
     constexpr uint32_t idesc = umma_idesc_bf16(128, BLOCK_N, 0, 0);
+    const uint32_t d_hi = desc_hi(8 * ROW_BYTES, ROW_BYTES);      // same geometry for A and B tiles
     int stage = 0;
     uint32_t phase = 0;
     for (int kb = 0; kb < num_kb; ++kb) {
       mbar_wait(&full_bar[stage], phase);
       tc_fence_after();
       const uint32_t sa = smem_u32(smem + stage * Cfg::STAGE_BYTES);
-      const uint32_t sb = sa + Cfg::A_BYTES;
+      const uint32_t a_lo = desc_lo(sa, 16), b_lo = desc_lo(sa + Cfg::A_BYTES, 16);
 #pragma unroll
-      for (int k = 0; k < CIN_BLK / 16; ++k) {
-        umma_bf16(tmem_base, smem_desc_kmajor(sa + k * 32, ROW_BYTES), smem_desc_kmajor(sb + k * 32, ROW_BYTES), idesc,
-                  (kb | k) != 0 ? 1u : 0u);
-      }
+      for (int k = 0; k < CIN_BLK / 16; ++k)
+        umma_bf16_split(tmem_base, a_lo + 2 * k, d_hi, b_lo + 2 * k, d_hi, idesc, (uint32_t)(kb | k));
       umma_commit(&empty_bar[stage]);  // frees this stage once the MMAs above have read it
       if (++stage == STAGES) { stage = 0; phase ^= 1; }
     }

@@ -106,22 +106,25 @@ __global__ void __launch_bounds__(192)
   } else if (threadIdx.x == 32) {
     // ===== MMA issuer =====
     const uint32_t idesc = umma_idesc_bf16(128, p.n_cols, 1, 1);
+    const uint32_t a_hi = desc_hi(8 * a_row_bytes, a_row_bytes), b_hi = desc_hi(8 * b_row_bytes, b_row_bytes);
+    const uint32_t a_kstep = (uint32_t)(16 * a_row_bytes) >> 4, b_kstep = (uint32_t)(16 * b_row_bytes) >> 4;
+    const uint32_t a_tstep = (uint32_t)a_tile_bytes >> 4;
+    const int ksteps = p.pix / 16;
     int stage = 0;
     uint32_t phase = 0;
-    bool first = true;
+    uint32_t first = 0;
     for (int t = t_beg; t < t_end; ++t) {
       mbar_wait(&full_bar[stage], phase);
       tc_fence_after();
       const uint32_t sb = smem_u32(smem + stage * stage_bytes);
-      const uint32_t sa = sb + b_bytes;
-      for (int m = 0; m < my_mt; ++m) {
-        for (int ks = 0; ks < p.pix / 16; ++ks) {
-          const uint64_t ad = smem_desc_mnmajor(sa + m * a_tile_bytes + ks * 16 * a_row_bytes, a_row_bytes, a_box_bytes);
-          const uint64_t bd = smem_desc_mnmajor(sb + ks * 16 * b_row_bytes, b_row_bytes, b_box_bytes);
-          umma_bf16(tmem_base + m * p.n_cols, ad, bd, idesc, (first && ks == 0) ? 0u : 1u);
-        }
+      const uint32_t b_lo0 = desc_lo(sb, (uint32_t)b_box_bytes);
+      uint32_t a_lo = desc_lo(sb + b_bytes, (uint32_t)a_box_bytes);
+      for (int m = 0; m < my_mt; ++m, a_lo += a_tstep) {
+        const uint32_t acc = tmem_base + m * p.n_cols;
+        for (int ks = 0; ks < ksteps; ++ks)
+          umma_bf16_split(acc, a_lo + ks * a_kstep, a_hi, b_lo0 + ks * b_kstep, b_hi, idesc, first | (uint32_t)ks);
       }
-      first = false;
+      first = 1;
       umma_commit(&empty_bar[stage]);
       if (++stage == p.stages) { stage = 0; phase ^= 1; }
     }

@@ -336,3 +336,33 @@ __device__ __forceinline__ void epilogue_tile(uint32_t tmem_tile, int q, int lan
 
 }  // namespace tc
 }  // namespace p2p
+
+// ---------------------------------------------------------------------------------------------------
+// Split descriptors for tight MMA issue loops.  One thread issues every MMA, and a dependent chain of
+// 64-bit descriptor arithmetic per instruction costs more cycles than a 128x128x16 MMA takes to execute
+// (measured: ~250 cycles/MMA issue vs 64 cycles of tensor work).  The high word of a shared-memory
+// descriptor (SBO, version, swizzle) is loop invariant; the low word is (address >> 4) | LBO << 16, so
+// stepping through taps / K slices is one 32-bit add.
+// ---------------------------------------------------------------------------------------------------
+namespace p2p {
+namespace tc {
+
+__device__ __forceinline__ uint32_t desc_hi(uint32_t sbo_bytes, int row_bytes) {
+  return ((sbo_bytes >> 4) & 0x3FFF) | (1u << 14) | (umma_layout_for_bytes(row_bytes) << 29);
+}
+__device__ __forceinline__ uint32_t desc_lo(uint32_t saddr, uint32_t lbo_bytes) {
+  return ((saddr >> 4) & 0x3FFF) | (((lbo_bytes >> 4) & 0x3FFF) << 16);
+}
+__device__ __forceinline__ void umma_bf16_split(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo,
+                                                uint32_t b_hi, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+      "mov.b64 da, {%1, %2};\n\tmov.b64 db, {%3, %4};\n\t"
+      "setp.ne.b32 p, %6, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}\n" ::"r"(tmem_d),
+      "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+}  // namespace tc
+}  // namespace p2p
