@@ -170,7 +170,20 @@ bool conv_wgrad_tc_supported(const p2p_conv* c) {
   return m_tiles * bpt <= kMaxSlots && c->kh <= 127 && c->kw <= 127;
 }
 
+// conv_wgrad_halo.cu
+bool conv_wgrad_halo_supported(const p2p_conv* c);
+int conv_wgrad_halo(const p2p_conv* c, const void* in, const void* dout, float* dw, cudaStream_t st);
+
 int conv_wgrad_tc(const p2p_conv* c, const void* in, const void* dout, float* dw, cudaStream_t st) {
+  static int no_halo = -1;
+  if (no_halo < 0) {
+    const char* e = getenv("P2P_NO_WGRAD_HALO");
+    no_halo = (e != nullptr && e[0] == '1') ? 1 : 0;
+  }
+  if (!no_halo && conv_wgrad_halo_supported(c)) {
+    const int rc = conv_wgrad_halo(c, in, dout, dw, st);   // stride-1 layers: one halo load per stage for all taps
+    if (rc != -2) return rc;
+  }
   WgParams p{};
   const int cin_blk = c->Ci >= 64 ? 64 : c->Ci;
   const int co_blk = c->Co >= 64 ? 64 : c->Co;
