@@ -109,9 +109,10 @@ int p2p_spectral_norm(int n_layers, const float* const* w_host, float* const* u_
  *     larger requests are rejected (<0, see p2p_last_error()) -- use p2p_spectral_norm with your own buffer;
  *   - the first call on each device looks up the array's device address; make that first call before
  *     starting any stream capture on that device.  No call allocates or frees memory;
- *   - all calls share the one array, and it keeps whatever the previous call left in it (the kernels
- *     overwrite every element before reading it, so nothing needs clearing).  Two calls whose kernels can
- *     overlap on the GPU -- different streams, or different host threads -- race on it: serialise them. */
+ *   - all calls share the one array, and it keeps whatever the previous call left in it; each call clears
+ *     the part it accumulates into (a memset enqueued on `stream`) before its first kernel.  Two calls
+ *     whose kernels can overlap on the GPU -- different streams, or different host threads -- race on it:
+ *     serialise them. */
 #define P2P_SN_STATIC_MAX_FLOATS 32768
 int p2p_spectral_norm_static(int n_layers, const float* const* w_host, float* const* u_host, float* const* v_host,
                              float* const* sigma_host, const int32_t* rows_host, const int32_t* cols_host,

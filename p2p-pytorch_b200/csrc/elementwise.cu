@@ -6,6 +6,8 @@
 
 namespace p2p {
 
+__device__ int g_dbg_no_atomics = 0;   // timing experiment switch (P2P_DEBUG_NO_RED_ATOMICS=1)
+
 // =================================================================================================
 // generator input: PixelUnshuffle(2) -> nearest x2 -> ReflectionPad(4)   (networks.py:173-187,457,399)
 // =================================================================================================
@@ -122,10 +124,11 @@ __device__ __forceinline__ float act_bwd(float z, int act, float a) {
 
 // y = act(scale*r + shift [+ skip]) -> padded / upsampled destination (gather form: one thread per
 // destination pixel x 8 channels, source found through the reflection and the >> log2(up)).
-template <typename T>
+template <typename T, int ACT>
 __global__ void bn_act_store_kernel(const T* __restrict__ r, const float* __restrict__ sb, const T* __restrict__ skip,
                                     int skip_pad, const float* __restrict__ prelu_a, T* __restrict__ dst, int B, int H,
-                                    int W, int C, int act, int up, int pad) {
+                                    int W, int C, int up, int pad) {
+  constexpr int act = ACT;
   const int C8 = C >> 3, Hu = H * up, Wu = W * up, Hd = Hu + 2 * pad, Wd = Wu + 2 * pad;
   const int sh = up == 2 ? 1 : 0;
   const float a = prelu_a != nullptr ? *prelu_a : 0.f;
@@ -172,22 +175,51 @@ __global__ void bn_act_store_nchw_kernel(const T* __restrict__ r, const float* _
   }
 }
 
-// rows of the padded buffer that mirror onto upsampled row u (besides u+pad itself)
-__device__ __forceinline__ void fold_candidates(int u, int n, int pad, int out[3]) {
-  out[0] = u + pad;
-  out[1] = (u >= 1 && u <= pad) ? pad - u : -1;                                   // top / left halo
-  out[2] = (u <= n - 2 && u >= n - 1 - pad) ? 2 * (n - 1) - u + pad : -1;         // bottom / right halo
+// raw 8-channel vector: lets a thread issue all of its loads before the first conversion / use
+template <typename T> struct Raw8;
+template <> struct Raw8<float> {
+  float4 a, b;
+  __device__ __forceinline__ void load(const float* p) {
+    a = reinterpret_cast<const float4*>(p)[0];
+    b = reinterpret_cast<const float4*>(p)[1];
+  }
+  __device__ __forceinline__ void zero() { a = make_float4(0.f, 0.f, 0.f, 0.f); b = a; }
+  __device__ __forceinline__ void get(float v[8]) const {
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  }
+};
+template <> struct Raw8<__nv_bfloat16> {
+  uint4 u;
+  __device__ __forceinline__ void load(const __nv_bfloat16* p) { u = *reinterpret_cast<const uint4*>(p); }
+  __device__ __forceinline__ void zero() { u = make_uint4(0u, 0u, 0u, 0u); }
+  __device__ __forceinline__ void get(float v[8]) const {
+    const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      v[2 * i] = __uint_as_float(w[i] << 16);
+      v[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u);
+    }
+  }
+};
+
+// rows of the padded buffer that mirror onto upsampled row u besides u+pad itself (-1 = none)
+__device__ __forceinline__ void fold_extra(int u, int n, int pad, int out[2]) {
+  out[0] = (u >= 1 && u <= pad) ? pad - u : -1;                                   // top / left halo
+  out[1] = (u <= n - 2 && u >= n - 1 - pad) ? 2 * (n - 1) - u + pad : -1;         // bottom / right halo
 }
 
 // backward pass 1 (see header).  One thread per source pixel x 8 channels; block = 256 threads laid out
 // as (C/8 channel groups) x (256/(C/8) pixel lanes) so the per-channel partial sums reduce through smem.
-template <typename T>
-__global__ void __launch_bounds__(256)
+// All loads of an item (up to 8 x 16 bytes) are issued before the first use; the reflection halo, which only
+// border pixels have, is a separate rarely-taken path.
+template <typename T, int ACT>
+__global__ void __launch_bounds__(256, 3)
     bn_act_bwd_reduce_kernel(const T* __restrict__ dpad, const T* __restrict__ g1, const T* __restrict__ g2,
                              const float* __restrict__ g_nchw, const T* __restrict__ r, const float* __restrict__ sb,
                              const T* __restrict__ skip, int skip_pad, const float* __restrict__ prelu_a,
                              T* __restrict__ dz, double* __restrict__ red, double* __restrict__ dprelu, int B, int H,
-                             int W, int C, int c_real, int act, int up, int pad) {
+                             int W, int C, int c_real, int up, int pad) {
+  constexpr int act = ACT;
   const int C8 = C >> 3;
   const int c8 = threadIdx.x % C8, lane_p = threadIdx.x / C8, ppb = 256 / C8;
   const int Hu = H * up, Wu = W * up, Hd = Hu + 2 * pad, Wd = Wu + 2 * pad;
@@ -197,49 +229,88 @@ __global__ void __launch_bounds__(256)
   float sa = 0.f;
 #pragma unroll
   for (int k = 0; k < 8; ++k) s1[k] = s2[k] = 0.f;
+  // per-channel constants of this thread
+  float sc[8], sh_[8], mean[8], istd[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int c = c8 * 8 + k;
+    sc[k] = sb != nullptr ? sb[c] : 1.f;
+    sh_[k] = sb != nullptr ? sb[C + c] : 0.f;
+    mean[k] = sb != nullptr ? sb[2 * C + c] : 0.f;
+    istd[k] = sb != nullptr ? sb[3 * C + c] : 0.f;
+  }
   for (uint32_t p = blockIdx.x * ppb + lane_p; p < pixels; p += gridDim.x * ppb) {
     const int x = (int)(p % (uint32_t)W);
     const uint32_t pq = p / (uint32_t)W;
     const int y = (int)(pq % (uint32_t)H);
     const int n = (int)(pq / (uint32_t)H);
-    float g[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) g[k] = 0.f;
+    // ---- issue every load first ----
+    Raw8<T> d00, d01, d10, d11, q1, q2, rr, sk;
+    d00.zero(); d01.zero(); d10.zero(); d11.zero(); q1.zero(); q2.zero(); sk.zero();
+    const T* dbase = nullptr;
     if (dpad != nullptr) {
-      // every padded position that mirrors / upsamples onto this source pixel; the interior case (one or
-      // up*up reads) is the common one, halo candidates are -1 away from the borders
-      for (int uy = y * up; uy < y * up + up; ++uy) {
-        int rows[3];
-        fold_candidates(uy, Hu, pad, rows);
-        for (int ux = x * up; ux < x * up + up; ++ux) {
-          int cols[3];
-          fold_candidates(ux, Wu, pad, cols);
+      dbase = dpad + (((int64_t)n * Hd + y * up + pad) * Wd + x * up + pad) * C + c8 * 8;
+      d00.load(dbase);
+      if (up == 2) {
+        d01.load(dbase + C);
+        d10.load(dbase + (int64_t)Wd * C);
+        d11.load(dbase + (int64_t)Wd * C + C);
+      }
+    }
+    if (g1 != nullptr) q1.load(g1 + (size_t)p * C + c8 * 8);
+    if (g2 != nullptr) q2.load(g2 + (size_t)p * C + c8 * 8);
+    rr.load(r + (size_t)p * C + c8 * 8);
+    if (skip != nullptr)
+      sk.load(skip + (((int64_t)n * (H + 2 * skip_pad) + y + skip_pad) * (W + 2 * skip_pad) + x + skip_pad) * C + c8 * 8);
+    // ---- combine ----
+    float g[8], t[8];
+    d00.get(g);
+    if (up == 2) {
+      d01.get(t);
 #pragma unroll
-          for (int a_ = 0; a_ < 3; ++a_) {
-            if (rows[a_] < 0) continue;
+      for (int k = 0; k < 8; ++k) g[k] += t[k];
+      d10.get(t);
 #pragma unroll
-            for (int b_ = 0; b_ < 3; ++b_) {
-              if (cols[b_] < 0) continue;
-              float t[8];
-              ld8(dpad + (((int64_t)n * Hd + rows[a_]) * Wd + cols[b_]) * C + c8 * 8, t);
+      for (int k = 0; k < 8; ++k) g[k] += t[k];
+      d11.get(t);
 #pragma unroll
-              for (int k = 0; k < 8; ++k) g[k] += t[k];
+      for (int k = 0; k < 8; ++k) g[k] += t[k];
+    }
+    q1.get(t);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) g[k] += t[k];
+    q2.get(t);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) g[k] += t[k];
+    // reflection halo: only pixels within `pad` of the border have mirrored copies
+    if (dpad != nullptr && pad > 0) {
+      const int uy0 = y * up, ux0 = x * up;
+      const bool near = uy0 <= pad || uy0 + up - 1 >= Hu - 1 - pad || ux0 <= pad || ux0 + up - 1 >= Wu - 1 - pad;
+      if (near) {
+        for (int uy = uy0; uy < uy0 + up; ++uy) {
+          int er[2];
+          fold_extra(uy, Hu, pad, er);
+          for (int ux = ux0; ux < ux0 + up; ++ux) {
+            int ec[2];
+            fold_extra(ux, Wu, pad, ec);
+            // (extra row, own col), (own row, extra col), (extra row, extra col)
+#pragma unroll
+            for (int ai = -1; ai < 2; ++ai) {
+              const int row = ai < 0 ? uy + pad : er[ai];
+              if (row < 0) continue;
+#pragma unroll
+              for (int bi = -1; bi < 2; ++bi) {
+                if (ai < 0 && bi < 0) continue;          // the interior copy was already added
+                const int col = bi < 0 ? ux + pad : ec[bi];
+                if (col < 0) continue;
+                ld8(dpad + (((int64_t)n * Hd + row) * Wd + col) * C + c8 * 8, t);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) g[k] += t[k];
+              }
             }
           }
         }
       }
-    }
-    if (g1 != nullptr) {
-      float t[8];
-      ld8(g1 + (size_t)p * C + c8 * 8, t);
-#pragma unroll
-      for (int k = 0; k < 8; ++k) g[k] += t[k];
-    }
-    if (g2 != nullptr) {
-      float t[8];
-      ld8(g2 + (size_t)p * C + c8 * 8, t);
-#pragma unroll
-      for (int k = 0; k < 8; ++k) g[k] += t[k];
     }
     if (g_nchw != nullptr) {
 #pragma unroll
@@ -248,22 +319,19 @@ __global__ void __launch_bounds__(256)
         if (c < c_real) g[k] += g_nchw[(((int64_t)n * c_real + c) * H + y) * W + x];
       }
     }
-    float rv[8], sk[8];
-    ld8(r + (size_t)p * C + c8 * 8, rv);
-    if (skip != nullptr)
-      ld8(skip + (((int64_t)n * (H + 2 * skip_pad) + y + skip_pad) * (W + 2 * skip_pad) + x + skip_pad) * C + c8 * 8, sk);
-    float o[8];
+    float rv[8], skv[8], o[8];
+    rr.get(rv);
+    sk.get(skv);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       const int c = c8 * 8 + k;
-      float z = sb != nullptr ? fmaf(rv[k], sb[c], sb[C + c]) : rv[k];
-      if (skip != nullptr) z += sk[k];
+      const float z = fmaf(rv[k], sc[k], sh_[k]) + skv[k];
       const float d = (c < c_real) ? g[k] * act_bwd(z, act, a) : 0.f;
       if (act == P2P_ACT_PRELU && z < 0.f && c < c_real) sa += g[k] * z;
       o[k] = d;
       const float dq = round_as(d, dz);
       s1[k] += dq;
-      if (sb != nullptr) s2[k] += dq * (rv[k] - sb[2 * C + c]) * sb[3 * C + c];
+      s2[k] += dq * (rv[k] - mean[k]) * istd[k];
     }
     st8(dz + (size_t)p * C + c8 * 8, o);
   }
@@ -276,7 +344,8 @@ __global__ void __launch_bounds__(256)
       const int which = t / C, c = t % C;
       double acc = 0.0;
       for (int l = 0; l < ppb; ++l) acc += (double)sh[which][c & 7][l * C8 + (c >> 3)];
-      atomicAdd(red + which * C + c, acc);
+      if (!g_dbg_no_atomics) atomicAdd(red + which * C + c, acc);
+      else if (acc == 1.2345) red[0] = acc;
     }
   }
   if (dprelu != nullptr && act == P2P_ACT_PRELU) {
@@ -615,9 +684,29 @@ int p2p_bn_act_store(const void* r, const float* sb, const void* skip, int skip_
   }
   const int64_t total = (int64_t)B * (H * up + 2 * pad) * (W * up + 2 * pad) * (C / 8);
   P2P_REQUIRE(total < (1LL << 31), "tensor too large");
-  P2P_DISPATCH(dtype, bn_act_store_kernel<T><<<ew_grid(total), 256, 0, as_stream(stream)>>>(
-                          (const T*)r, sb, (const T*)skip, skip_pad, prelu_a, (T*)dst, B, H, W, C, act, up, pad););
+#define P2P_STORE(ACT_)                                                                            \
+  P2P_DISPATCH(dtype, bn_act_store_kernel<T, ACT_><<<ew_grid(total), 256, 0, as_stream(stream)>>>( \
+                          (const T*)r, sb, (const T*)skip, skip_pad, prelu_a, (T*)dst, B, H, W, C, up, pad););
+  switch (act) {
+    case P2P_ACT_NONE: P2P_STORE(P2P_ACT_NONE) break;
+    case P2P_ACT_RELU: P2P_STORE(P2P_ACT_RELU) break;
+    case P2P_ACT_PRELU: P2P_STORE(P2P_ACT_PRELU) break;
+    case P2P_ACT_LRELU: P2P_STORE(P2P_ACT_LRELU) break;
+    case P2P_ACT_TANH: P2P_STORE(P2P_ACT_TANH) break;
+    default: P2P_REQUIRE(false, "unknown activation");
+  }
+#undef P2P_STORE
   P2P_LAUNCH_CHECK();
+}
+
+static void dbg_init() {
+  static bool done = false;
+  if (!done) {
+    const char* e = getenv("P2P_DEBUG_NO_RED_ATOMICS");
+    const int v = (e != nullptr && e[0] == '1') ? 1 : 0;
+    cudaMemcpyToSymbol(p2p::g_dbg_no_atomics, &v, sizeof(int));
+    done = true;
+  }
 }
 
 int p2p_bn_act_bwd_reduce(const void* dpad, const void* g1, const void* g2, const float* g_nchw, const void* r,
@@ -630,10 +719,21 @@ int p2p_bn_act_bwd_reduce(const void* dpad, const void* g1, const void* g2, cons
   P2P_REQUIRE(act != P2P_ACT_PRELU || prelu_a, "PReLU needs its slope");
   const int ppb = 256 / (C / 8);
   const int64_t pixels = (int64_t)B * H * W;
+  dbg_init();
   P2P_REQUIRE((int64_t)B * (H * up + 2 * pad) * (W * up + 2 * pad) * (C / 8) < (1LL << 31), "tensor too large");
-  P2P_DISPATCH(dtype, bn_act_bwd_reduce_kernel<T><<<red_ew_grid(pixels, ppb), 256, 0, as_stream(stream)>>>(
-                          (const T*)dpad, (const T*)g1, (const T*)g2, g_nchw, (const T*)r, sb, (const T*)skip, skip_pad,
-                          prelu_a, (T*)dz, red, dprelu, B, H, W, C, c_real, act, up, pad););
+#define P2P_BWD_REDUCE(ACT_)                                                                                     \
+  P2P_DISPATCH(dtype, bn_act_bwd_reduce_kernel<T, ACT_><<<red_ew_grid(pixels, ppb), 256, 0, as_stream(stream)>>>( \
+                          (const T*)dpad, (const T*)g1, (const T*)g2, g_nchw, (const T*)r, sb, (const T*)skip, skip_pad, \
+                          prelu_a, (T*)dz, red, dprelu, B, H, W, C, c_real, up, pad););
+  switch (act) {
+    case P2P_ACT_NONE: P2P_BWD_REDUCE(P2P_ACT_NONE) break;
+    case P2P_ACT_RELU: P2P_BWD_REDUCE(P2P_ACT_RELU) break;
+    case P2P_ACT_PRELU: P2P_BWD_REDUCE(P2P_ACT_PRELU) break;
+    case P2P_ACT_LRELU: P2P_BWD_REDUCE(P2P_ACT_LRELU) break;
+    case P2P_ACT_TANH: P2P_BWD_REDUCE(P2P_ACT_TANH) break;
+    default: P2P_REQUIRE(false, "unknown activation");
+  }
+#undef P2P_BWD_REDUCE
   P2P_LAUNCH_CHECK();
 }
 

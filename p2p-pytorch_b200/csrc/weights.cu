@@ -80,17 +80,21 @@ struct SnTable {
   int tmp_off[P2P_SN_MAX_LAYERS];  // offset of this layer's scratch (cols + rows floats)
 };
 
-// t[k] = sum_r W[r][k] u[r]      grid (ceil(cols/256), layers)
+// t[k] += sum over a 32-row slab of W[r][k] u[r]      grid (ceil(cols/256), layers, ceil(max_rows/32));
+// t is zeroed first (cudaMemsetAsync); 16x more CTAs than one thread per column over all rows
 __global__ void sn_wt_u_kernel(SnTable tb, float* __restrict__ tmp) {
   const int l = blockIdx.y;
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   const int rows = tb.rows[l], cols = tb.cols[l];
-  if (k >= cols) return;
-  const float* w = tb.w[l];
-  const float* u = tb.u[l];
+  const int r0 = blockIdx.z * 32;
+  if (k >= cols || r0 >= rows) return;
+  const float* w = tb.w[l] + (int64_t)r0 * cols + k;
+  const float* u = tb.u[l] + r0;
+  const int nr = min(32, rows - r0);
   float acc = 0.f;
-  for (int r = 0; r < rows; ++r) acc = fmaf(w[(int64_t)r * cols + k], u[r], acc);
-  tmp[tb.tmp_off[l] + k] = acc;
+#pragma unroll 8
+  for (int r = 0; r < nr; ++r) acc = fmaf(w[(int64_t)r * cols], u[r], acc);
+  atomicAdd(tmp + tb.tmp_off[l] + k, acc);
 }
 
 // v = t / (|t| + eps)            grid (layers), block 1024
@@ -199,7 +203,8 @@ int p2p_spectral_norm(int n_layers, const float* const* w_host, float* const* u_
     max_cols = cols_host[l] > max_cols ? cols_host[l] : max_cols;
   }
   cudaStream_t st = as_stream(stream);
-  sn_wt_u_kernel<<<dim3(cdiv(max_cols, 256), n_layers), 256, 0, st>>>(tb, tmp);
+  P2P_CUDA(cudaMemsetAsync(tmp, 0, sizeof(float) * (size_t)off, st));
+  sn_wt_u_kernel<<<dim3(cdiv(max_cols, 256), n_layers, cdiv(max_rows, 32)), 256, 0, st>>>(tb, tmp);
   sn_norm_v_kernel<<<n_layers, 1024, 0, st>>>(tb, tmp);
   sn_w_v_kernel<<<dim3(cdiv(max_rows, 8), n_layers), 256, 0, st>>>(tb, tmp);
   sn_norm_u_kernel<<<n_layers, 512, 0, st>>>(tb, tmp);
@@ -263,7 +268,8 @@ extern "C" int p2p_spectral_norm_static(int n_layers, const float* const* w_host
                   std::to_string(P2P_SN_STATIC_MAX_FLOATS) + " floats: use p2p_spectral_norm with your own buffer");
   float* scratch = nullptr;
   if (int e = sn_static_scratch(&scratch)) return e;
-  // Nothing in the scratch has to start at zero: every element a kernel reads was written earlier in the
-  // same call (W^T u fills [0, cols), W v fills [cols, cols + rows) of each layer's slice).
+  // The array still holds whatever the previous call left in it.  The W^T u partial sums are accumulated with
+  // atomics and must start from zero: p2p_spectral_norm clears the part of the scratch it uses (a memset on
+  // `stream`, no allocation) before its first kernel; W v then overwrites its slice before anything reads it.
   return p2p_spectral_norm(n_layers, w_host, u_host, v_host, sigma_host, rows_host, cols_host, scratch, stream);
 }

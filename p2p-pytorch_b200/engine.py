@@ -91,9 +91,14 @@ class ConvPlan:
         call("p2p_conv_dgrad", C.byref(self.desc), ptr(dout), ptr(self.wt), ptr(din), L.dtype_code(dout.dtype),
              _state["impl"])
 
-    def wgrad(self, x, dout, grad, sigma=None, dot=None, w_for_dot=None):
-        """grad ([co][ci][kh][kw] fp32) += d loss / d weight  (scaled by 1/sigma if given)"""
-        acc = _zeros((self.k, self.k, self.Ci, self.Co), torch.float32, x.device)
+    def acc_numel(self):
+        return self.k * self.k * self.Ci * self.Co
+
+    def wgrad(self, x, dout, grad, sigma=None, dot=None, w_for_dot=None, acc=None):
+        """grad ([co][ci][kh][kw] fp32) += d loss / d weight  (scaled by 1/sigma if given).
+        `acc`: zeroed fp32 scratch of acc_numel() elements (callers zero one slab for all their layers)."""
+        if acc is None:
+            acc = _zeros((self.acc_numel(),), torch.float32, x.device)
         call("p2p_conv_wgrad", C.byref(self.desc), ptr(x), ptr(dout), ptr(acc), L.dtype_code(x.dtype), _state["impl"])
         call("p2p_unpack_wgrad", ptr(acc), ptr(grad), ptr(w_for_dot), ptr(sigma), ptr(dot), self.cout_real,
              self.cin_real, self.Co, self.Ci, self.k, self.k)
@@ -228,6 +233,20 @@ class GeneratorFunction(torch.autograd.Function):
         dc = L.dtype_code(dt)
         g_out = g_out.contiguous().float()
         dprelu = _zeros((1,), torch.float64, dev)
+        # one zeroed slab for all split-K weight-gradient accumulators and BatchNorm reductions of this pass
+        acc_sizes = [st.plan.acc_numel() for st in stages if st.plan is not None]
+        acc_slab = _zeros((sum(acc_sizes),), torch.float32, dev)
+        acc_off = {}
+        off = 0
+        for st in stages:
+            if st.plan is not None:
+                acc_off[id(st)] = off
+                off += st.plan.acc_numel()
+        red_slab = _zeros((sum(2 * st.C for st in stages),), torch.float64, dev)
+        red_off, off = {}, 0
+        for st in stages:
+            red_off[id(st)] = off
+            off += 2 * st.C
         ret: List[Optional[torch.Tensor]] = [None] * (4 * G_N)
         dpad = None            # gradient w.r.t. the (padded) buffer the stage being processed wrote
         extra = {}             # id(stage) -> compact gradients addressed to that stage's output (skip paths)
@@ -245,7 +264,7 @@ class GeneratorFunction(torch.autograd.Function):
                 continue
             li = st.li
             pw, pb, pg, pbeta = refs[1 + 4 * li: 5 + 4 * li]
-            red = _zeros((2 * st.C,), torch.float64, dev)
+            red = red_slab[red_off[id(st)]: red_off[id(st)] + 2 * st.C]
             call("p2p_bn_act_bwd_reduce", ptr(dpad), ptr(g1), ptr(g2), ptr(g_out) if li == G_N - 1 else None, ptr(st.r),
                  ptr(st.sb), ptr(st.skip), st.skip_pad, ptr(prelu), ptr(dz), ptr(red), ptr(dprelu), B, st.H, st.W, st.C,
                  st.c_real, st.act, st.up, st.pad, dc)
@@ -258,7 +277,7 @@ class GeneratorFunction(torch.autograd.Function):
             gbe, ret[4 * li + 3] = _grad_slot(pbeta)
             call("p2p_bn_bwd_apply", ptr(dz), ptr(st.r), ptr(st.sb), ptr(red), ptr(dr), ptr(gg), ptr(gbe), ptr(gb),
                  B * st.H * st.W, st.C, st.c_real, dc)
-            st.plan.wgrad(st.x_in, dr, gw)
+            st.plan.wgrad(st.x_in, dr, gw, acc=acc_slab[acc_off[id(st)]: acc_off[id(st)] + st.plan.acc_numel()])
             if li > 0:
                 dpad = _empty(tuple(st.x_in.shape), dt, dev)
                 st.plan.dgrad(dr, dpad)
@@ -377,6 +396,13 @@ class DiscriminatorFunction(torch.autograd.Function):
         need_bias = [ctx.needs_input_grad[4 + 2 * k] for k in range(NUM_D * nl)]
         ret: List[Optional[torch.Tensor]] = [None] * (2 * NUM_D * nl)
         sn_pos = {key: i for i, key in enumerate(ctx.sn_idx)}
+        acc_slab, acc_offs = None, []
+        if any(need_w):
+            off = 0
+            for pl in plans:
+                acc_offs.append(off)
+                off += pl.acc_numel()
+            acc_slab = _zeros((off,), torch.float32, dev)
         dx32 = [None] * NUM_D       # fp32 gradient of each pyramid level (only when need_b)
         for i in reversed(range(NUM_D)):
             sc = NUM_D - 1 - i
@@ -406,12 +432,13 @@ class DiscriminatorFunction(torch.autograd.Function):
                         sigma = ctx.sig_of[(sc, j)]
                         dot = _zeros((1,), torch.float32, dev)
                         # gW_bar = gW / sigma - (sum gW * W_bar) / sigma^2 * u v^T   (W = W_bar / sigma)
-                        plan.wgrad(x_in, dz, gw, sigma=sigma, dot=dot, w_for_dot=pw.detach())
+                        plan.wgrad(x_in, dz, gw, sigma=sigma, dot=dot, w_for_dot=pw.detach(),
+                                   acc=acc_slab[acc_offs[idx]: acc_offs[idx] + plan.acc_numel()])
                         u, v = ctx.sn_bufs[sn_pos[(sc, j)]]      # read NOW, not at forward: quirk Q1
                         call("p2p_sn_weight_grad", ptr(gw), ptr(dot), ptr(sigma), ptr(u), ptr(v), pw.shape[0],
                              pw[0].numel())
                     else:
-                        plan.wgrad(x_in, dz, gw)
+                        plan.wgrad(x_in, dz, gw, acc=acc_slab[acc_offs[idx]: acc_offs[idx] + plan.acc_numel()])
                 if j > 0 or need_b:
                     g_next = _empty(tuple(x_in.shape), dt, dev)
                     plan.dgrad(dz, g_next)
