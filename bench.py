@@ -49,7 +49,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -148,15 +148,16 @@ def time_dominant_kernel(P, B, S, iters=20):
 def run_ours(args, rank, world, local_rank):
     import torch.distributed as dist
     import p2p_pytorch_b200 as P
-    from oracle import pix2pix_oracle as orc   # only for the deterministic initial weights / data generator and cpu_baseline
+    import contextlib
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     B, S = args.batch, args.size
     P.set_precision(args.precision)
-    g = P.ExpandNetwork().to(dev)
-    d = P.MultiscaleDiscriminator(6, 64, getIntermFeat=True).to(dev)
-    g.load_state_dict(orc.init_g_state(123))
-    d.load_state_dict(orc.init_d_state(124))
+    torch.manual_seed(123)                                   # the reference's default --seed (train.py:155)
+    torch.cuda.manual_seed(123)
+    with contextlib.redirect_stdout(sys.stderr):             # init_weights prints, like the reference's
+        g = P.define_G("normal", 0.02, gpu_id=dev)
+        d = P.define_D(6, 64, gpu_id=dev)
     g.train(); d.train()
     tr = P.Pix2PixTrainer(g, d)
     tr.broadcast_parameters(0)
@@ -244,13 +245,17 @@ def run_ours(args, rank, world, local_rank):
         kms, kflops = time_dominant_kernel(P, B, S)
         ach = kflops / (kms * 1e-3) / 1e12
         line["roofline"] = {"bound": "tensor", "achieved": ach, "peak": tf_burst, "unit": "TFLOP/s",
-                            "frac": ach / tf_burst, "traffic": None, "peak_source": which,
+                            "frac": ach / tf_burst,
+                            # dram__bytes_read.sum + dram__bytes_write.sum of this launch, ncu --set full
+                            # (profiles/r01c_ncu_dominant_kernels.md); valid for the default B=16, 256x256 shape only
+                            "traffic": 18.16e6 if (B == 16 and S == 256) else None, "peak_source": which,
                             "kernel": "conv_tc_kernel<128,64> (3x3 128->128 residual conv fwd, bf16, fp32 accumulate)",
                             "ms_per_launch": kms}
     except Exception as e:                                   # e.g. fp32 verification mode: no tensor-core kernel
         line["roofline"] = {"bound": "tensor", "achieved": None, "peak": tf_burst, "unit": "TFLOP/s", "frac": None,
                             "traffic": None, "note": f"dominant-kernel timing unavailable: {e}"}
     if world == 1 and not args.no_cpu_baseline:
+        from oracle import pix2pix_oracle as orc             # the CPU checker, timed as the reported baseline only
         cores = os.cpu_count() or 1
         torch.set_num_threads(cores)
         otr = orc.OracleTrainer(orc.init_g_state(123), orc.init_d_state(124))
@@ -271,7 +276,7 @@ def run_ours(args, rank, world, local_rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=16, help="images per GPU")
