@@ -80,7 +80,10 @@ __global__ void __launch_bounds__(224, 1)
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
 
-  if (threadIdx.x == 0) {
+  // Role branches are WARP-uniform and the single issuing lane is chosen with elect.sync inside them: with a
+  // per-thread branch (threadIdx.x == k) the compiler cannot keep TMA / MMA operands in uniform registers and
+  // wraps every UTMALDG / UTCHMMA in a lane-serialising loop.
+  if (warp == 0) {
     // ===== halo producer: one box per (item, channel chunk) =====
     int ab = 0;
     uint32_t aph = 0;
@@ -90,19 +93,25 @@ __global__ void __launch_bounds__(224, 1)
       const int oy0 = (br / p.blocks_w) * 32, ox0 = (br % p.blocks_w) * 8;
       for (int c = 0; c < p.c_chunks; ++c) {
         mbar_wait(&a_empty[ab], aph ^ 1);
-        mbar_arrive_expect_tx(&a_full[ab], (uint32_t)(p.HH * p.HW * RB));
-        tma_load_4d(sA + ab * p.a_bytes, &map_a, &a_full[ab], c * CIN_BLK, ox0 + p.min_dw, oy0 + p.min_dh, img);
+        if (elect_one()) {
+          mbar_arrive_expect_tx(&a_full[ab], (uint32_t)(p.HH * p.HW * RB));
+          tma_load_4d(sA + ab * p.a_bytes, &map_a, &a_full[ab], c * CIN_BLK, ox0 + p.min_dw, oy0 + p.min_dh, img);
+        }
+        __syncwarp();
         if (++ab == NA) { ab = 0; aph ^= 1; }
       }
     }
-  } else if (threadIdx.x == 192) {
+  } else if (warp == 6) {
     // ===== weight producer =====
     if (p.resident) {
       // the whole filter bank once: tile (c, t) lives at sB + (c * n_taps + t) * B_BYTES for the kernel's lifetime
-      mbar_arrive_expect_tx(&b_full[0], (uint32_t)(p.c_chunks * p.n_taps * B_BYTES));
-      for (int c = 0; c < p.c_chunks; ++c)
-        for (int t = 0; t < p.n_taps; ++t)
-          tma_load_2d(sB + (c * p.n_taps + t) * B_BYTES, &map_b, &b_full[0], p.taps[t].wk + c * CIN_BLK, 0);
+      if (elect_one()) {
+        mbar_arrive_expect_tx(&b_full[0], (uint32_t)(p.c_chunks * p.n_taps * B_BYTES));
+        for (int c = 0; c < p.c_chunks; ++c)
+          for (int t = 0; t < p.n_taps; ++t)
+            tma_load_2d(sB + (c * p.n_taps + t) * B_BYTES, &map_b, &b_full[0], p.taps[t].wk + c * CIN_BLK, 0);
+      }
+      __syncwarp();
     } else {
       int bs = 0;
       uint32_t bph = 0;
@@ -111,14 +120,17 @@ __global__ void __launch_bounds__(224, 1)
         for (int c = 0; c < p.c_chunks; ++c)
           for (int t = 0; t < p.n_taps; ++t) {
             mbar_wait(&b_empty[bs], bph ^ 1);
-            mbar_arrive_expect_tx(&b_full[bs], B_BYTES);
-            tma_load_2d(sB + bs * B_BYTES, &map_b, &b_full[bs], p.taps[t].wk + c * CIN_BLK, n0);
+            if (elect_one()) {
+              mbar_arrive_expect_tx(&b_full[bs], B_BYTES);
+              tma_load_2d(sB + bs * B_BYTES, &map_b, &b_full[bs], p.taps[t].wk + c * CIN_BLK, n0);
+            }
+            __syncwarp();
             if (++bs == p.nb) { bs = 0; bph ^= 1; }
           }
       }
     }
-  } else if (threadIdx.x == 32) {
-    // ===== MMA issuer =====
+  } else if (warp == 1) {
+    // ===== MMA issuer (whole warp walks the loops, one elected lane issues) =====
     constexpr uint32_t idesc = umma_idesc_bf16(128, BLOCK_N, 0, 0);
     const uint32_t a_hi = desc_hi((uint32_t)(p.HW * RB), RB);     // 8-row groups of the tile are HW halo rows apart
     const uint32_t b_hi = desc_hi(8 * RB, RB);
@@ -144,23 +156,28 @@ __global__ void __launch_bounds__(224, 1)
             b_lo = desc_lo(smem_u32(sB + bs * B_BYTES), 16);
           }
           const uint32_t a_lo = a_lo0 + (uint32_t)p.taps[t].row_off16;
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < CIN_BLK / 16; ++k) {
-            umma_bf16_split(acc, a_lo + 2 * k, a_hi, b_lo + 2 * k, b_hi, idesc, first | (uint32_t)k);
-            umma_bf16_split(acc + BLOCK_N, a_lo + h_step + 2 * k, a_hi, b_lo + 2 * k, b_hi, idesc, first | (uint32_t)k);
+            for (int k = 0; k < CIN_BLK / 16; ++k) {
+              umma_bf16_split(acc, a_lo + 2 * k, a_hi, b_lo + 2 * k, b_hi, idesc, first | (uint32_t)k);
+              umma_bf16_split(acc + BLOCK_N, a_lo + h_step + 2 * k, a_hi, b_lo + 2 * k, b_hi, idesc, first | (uint32_t)k);
+            }
+            if (!p.resident) umma_commit(&b_empty[bs]);
           }
+          __syncwarp();
           first = 1;
           if (!p.resident) {
-            umma_commit(&b_empty[bs]);
             if (++bs == p.nb) { bs = 0; bph ^= 1; }
           } else {
             b_lo += B_BYTES >> 4;
           }
         }
-        umma_commit(&a_empty[ab]);
+        if (elect_one()) umma_commit(&a_empty[ab]);
+        __syncwarp();
         if (++ab == NA) { ab = 0; aph ^= 1; }
       }
-      umma_commit(&t_full[set]);
+      if (elect_one()) umma_commit(&t_full[set]);
+      __syncwarp();
     }
   } else if (warp >= 2 && warp <= 5) {
     // ===== epilogue =====

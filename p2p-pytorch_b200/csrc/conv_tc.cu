@@ -97,21 +97,24 @@ __global__ void __launch_bounds__(192)
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
 
-  if (threadIdx.x == 0) {
-    // ===== TMA producer =====
+  if (warp == 0) {
+    // ===== TMA producer (warp-uniform loop, one elected lane issues: keeps TMA operands in uniform registers) =====
     int stage = 0;
     uint32_t phase = 0;
     for (int kb = 0; kb < num_kb; ++kb) {
       const int tap = kb / p.c_chunks, cc = kb - tap * p.c_chunks;
       mbar_wait(&empty_bar[stage], phase ^ 1);
-      mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
-      uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
-      tma_load_4d(sa, &map_a, &full_bar[stage], cc * CIN_BLK, ox0 * p.in_mul + p.taps[tap].dw,
-                  oy0 * p.in_mul + p.taps[tap].dh, n_img);
-      tma_load_2d(sa + Cfg::A_BYTES, &map_b, &full_bar[stage], p.taps[tap].wk + cc * CIN_BLK, n0);
+      if (elect_one()) {
+        mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
+        uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
+        tma_load_4d(sa, &map_a, &full_bar[stage], cc * CIN_BLK, ox0 * p.in_mul + p.taps[tap].dw,
+                    oy0 * p.in_mul + p.taps[tap].dh, n_img);
+        tma_load_2d(sa + Cfg::A_BYTES, &map_b, &full_bar[stage], p.taps[tap].wk + cc * CIN_BLK, n0);
+      }
+      __syncwarp();
       if (++stage == STAGES) { stage = 0; phase ^= 1; }
     }
-  } else if (threadIdx.x == 32) {
+  } else if (warp == 1) {
     // ===== MMA issuer =====
     constexpr uint32_t idesc = umma_idesc_bf16(128, BLOCK_N, 0, 0);
     const uint32_t d_hi = desc_hi(8 * ROW_BYTES, ROW_BYTES);      // same geometry for A and B tiles
@@ -122,13 +125,17 @@ __global__ void __launch_bounds__(192)
       tc_fence_after();
       const uint32_t sa = smem_u32(smem + stage * Cfg::STAGE_BYTES);
       const uint32_t a_lo = desc_lo(sa, 16), b_lo = desc_lo(sa + Cfg::A_BYTES, 16);
+      if (elect_one()) {
 #pragma unroll
-      for (int k = 0; k < CIN_BLK / 16; ++k)
-        umma_bf16_split(tmem_base, a_lo + 2 * k, d_hi, b_lo + 2 * k, d_hi, idesc, (uint32_t)(kb | k));
-      umma_commit(&empty_bar[stage]);  // frees this stage once the MMAs above have read it
+        for (int k = 0; k < CIN_BLK / 16; ++k)
+          umma_bf16_split(tmem_base, a_lo + 2 * k, d_hi, b_lo + 2 * k, d_hi, idesc, (uint32_t)(kb | k));
+        umma_commit(&empty_bar[stage]);  // frees this stage once the MMAs above have read it
+      }
+      __syncwarp();
       if (++stage == STAGES) { stage = 0; phase ^= 1; }
     }
-    umma_commit(&tmem_full_bar);
+    if (elect_one()) umma_commit(&tmem_full_bar);
+    __syncwarp();
   } else if (warp >= 2) {
     // ===== epilogue =====
     mbar_wait(&tmem_full_bar, 0);

@@ -82,7 +82,7 @@ __global__ void __launch_bounds__(192, 1)
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
 
-  if (threadIdx.x == 0) {
+  if (warp == 0) {
     // ===== TMA producer: x halo (all channel chunks) + dy block per stage =====
     int stage = 0;
     uint32_t phase = 0;
@@ -92,16 +92,19 @@ __global__ void __launch_bounds__(192, 1)
       const int r = t - n * (p.blocks_w * p.blocks_h);
       const int oy0 = (r / p.blocks_w) * kWhRows, ox0 = (r % p.blocks_w) * kWhCols;
       mbar_wait(&empty_bar[stage], phase ^ 1);
-      mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
-      uint8_t* sx = smem + stage * p.stage_bytes;
-      for (int c = 0; c < p.n_chunks; ++c)
-        tma_load_4d(sx + c * p.x_bytes, &map_x, &full_bar[stage], c * p.cin_blk, ox0 + p.min_dw, oy0 + p.min_dh, n);
-      uint8_t* sy = sx + x_total;
-      for (int b = 0; b < p.b_boxes; ++b)
-        tma_load_4d(sy + b * dy_box, &map_dy, &full_bar[stage], co0 + b * p.co_blk, ox0, oy0, n);
+      if (elect_one()) {
+        mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
+        uint8_t* sx = smem + stage * p.stage_bytes;
+        for (int c = 0; c < p.n_chunks; ++c)
+          tma_load_4d(sx + c * p.x_bytes, &map_x, &full_bar[stage], c * p.cin_blk, ox0 + p.min_dw, oy0 + p.min_dh, n);
+        uint8_t* sy = sx + x_total;
+        for (int b = 0; b < p.b_boxes; ++b)
+          tma_load_4d(sy + b * dy_box, &map_dy, &full_bar[stage], co0 + b * p.co_blk, ox0, oy0, n);
+      }
+      __syncwarp();
       if (++stage == p.stages) { stage = 0; phase ^= 1; }
     }
-  } else if (threadIdx.x == 32) {
+  } else if (warp == 1) {
     // ===== MMA issuer =====
     const uint32_t idesc = umma_idesc_bf16(128, p.n_cols, 1, 1);
     const uint32_t a_hi = desc_hi(8 * rbx, rbx), b_hi = desc_hi(8 * rby, rby);
@@ -116,18 +119,22 @@ __global__ void __launch_bounds__(192, 1)
       const uint32_t sx = smem_u32(smem + stage * p.stage_bytes);
       const uint32_t x_lo = (sx >> 4) & 0x3FFF;
       const uint32_t y_lo = (((sx + x_total) >> 4) & 0x3FFF) | b_lbo;
-      for (int m = 0; m < my_mt; ++m) {
-        const uint32_t a_lo = x_lo + p.tiles[mt0 + m].lo_const;
-        const uint32_t acc = tmem_base + m * p.n_cols;
+      if (elect_one()) {
+        for (int m = 0; m < my_mt; ++m) {
+          const uint32_t a_lo = x_lo + p.tiles[mt0 + m].lo_const;
+          const uint32_t acc = tmem_base + m * p.n_cols;
 #pragma unroll
-        for (int y = 0; y < kWhRows; ++y)
-          umma_bf16_split(acc, a_lo + y * a_ystep, a_hi, y_lo + y * b_ystep, b_hi, idesc, first | (uint32_t)y);
+          for (int y = 0; y < kWhRows; ++y)
+            umma_bf16_split(acc, a_lo + y * a_ystep, a_hi, y_lo + y * b_ystep, b_hi, idesc, first | (uint32_t)y);
+        }
+        umma_commit(&empty_bar[stage]);
       }
+      __syncwarp();
       first = 1;
-      umma_commit(&empty_bar[stage]);
       if (++stage == p.stages) { stage = 0; phase ^= 1; }
     }
-    umma_commit(&tmem_full_bar);
+    if (elect_one()) umma_commit(&tmem_full_bar);
+    __syncwarp();
   } else if (warp >= 2 && t_end > t_beg) {
     // ===== epilogue: TMEM -> red.global.add.f32x4 =====
     const int q = warp & 3;
