@@ -85,22 +85,22 @@ __global__ void __launch_bounds__(224, 1)
   // wraps every UTMALDG / UTCHMMA in a lane-serialising loop.
   if (warp == 0) {
     // ===== halo producer: one box per (item, channel chunk) =====
-    int ab = 0;
-    uint32_t aph = 0;
-    for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
-      const int r = it % items_per_ntile;
-      const int img = r / blocks_per_img, br = r % blocks_per_img;
-      const int oy0 = (br / p.blocks_w) * 32, ox0 = (br % p.blocks_w) * 8;
-      for (int c = 0; c < p.c_chunks; ++c) {
-        mbar_wait(&a_empty[ab], aph ^ 1);
-        if (elect_one()) {
+    if (elect_one()) {
+      int ab = 0;
+      uint32_t aph = 0;
+      for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+        const int r = it % items_per_ntile;
+        const int img = r / blocks_per_img, br = r % blocks_per_img;
+        const int oy0 = (br / p.blocks_w) * 32, ox0 = (br % p.blocks_w) * 8;
+        for (int c = 0; c < p.c_chunks; ++c) {
+          mbar_wait(&a_empty[ab], aph ^ 1);
           mbar_arrive_expect_tx(&a_full[ab], (uint32_t)(p.HH * p.HW * RB));
           tma_load_4d(sA + ab * p.a_bytes, &map_a, &a_full[ab], c * CIN_BLK, ox0 + p.min_dw, oy0 + p.min_dh, img);
+          if (++ab == NA) { ab = 0; aph ^= 1; }
         }
-        __syncwarp();
-        if (++ab == NA) { ab = 0; aph ^= 1; }
       }
     }
+    __syncwarp();
   } else if (warp == 6) {
     // ===== weight producer =====
     if (p.resident) {
@@ -113,21 +113,21 @@ __global__ void __launch_bounds__(224, 1)
       }
       __syncwarp();
     } else {
-      int bs = 0;
-      uint32_t bph = 0;
-      for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
-        const int n0 = (it / items_per_ntile) * BLOCK_N;
-        for (int c = 0; c < p.c_chunks; ++c)
-          for (int t = 0; t < p.n_taps; ++t) {
-            mbar_wait(&b_empty[bs], bph ^ 1);
-            if (elect_one()) {
+      if (elect_one()) {
+        int bs = 0;
+        uint32_t bph = 0;
+        for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+          const int n0 = (it / items_per_ntile) * BLOCK_N;
+          for (int c = 0; c < p.c_chunks; ++c)
+            for (int t = 0; t < p.n_taps; ++t) {
+              mbar_wait(&b_empty[bs], bph ^ 1);
               mbar_arrive_expect_tx(&b_full[bs], B_BYTES);
               tma_load_2d(sB + bs * B_BYTES, &map_b, &b_full[bs], p.taps[t].wk + c * CIN_BLK, n0);
+              if (++bs == p.nb) { bs = 0; bph ^= 1; }
             }
-            __syncwarp();
-            if (++bs == p.nb) { bs = 0; bph ^= 1; }
-          }
+        }
       }
+      __syncwarp();
     }
   } else if (warp == 1) {
     // ===== MMA issuer (whole warp walks the loops, one elected lane issues) =====
@@ -149,28 +149,47 @@ __global__ void __launch_bounds__(224, 1)
         tc_fence_after();
         const uint32_t a_lo0 = desc_lo(smem_u32(sA + ab * p.a_bytes), 16);
         uint32_t b_lo = desc_lo(smem_u32(sB + (p.resident ? c * p.n_taps : 0) * B_BYTES), 16);
-        for (int t = 0; t < p.n_taps; ++t) {
-          if (!p.resident) {
-            mbar_wait(&b_full[bs], bph);
-            tc_fence_after();
-            b_lo = desc_lo(smem_u32(sB + bs * B_BYTES), 16);
-          }
-          const uint32_t a_lo = a_lo0 + (uint32_t)p.taps[t].row_off16;
+        if (p.resident) {
+          // no barriers inside: the elected lane walks all taps of this chunk back to back
           if (elect_one()) {
+#pragma unroll 3
+            for (int t = 0; t < p.n_taps; ++t) {
+              const uint32_t a_lo = a_lo0 + (uint32_t)p.taps[t].row_off16;
 #pragma unroll
-            for (int k = 0; k < CIN_BLK / 16; ++k) {
-              umma_bf16_split(acc, a_lo + 2 * k, a_hi, b_lo + 2 * k, b_hi, idesc, first | (uint32_t)k);
-              umma_bf16_split(acc + BLOCK_N, a_lo + h_step + 2 * k, a_hi, b_lo + 2 * k, b_hi, idesc, first | (uint32_t)k);
+              for (int k = 0; k < CIN_BLK / 16; ++k) {
+                umma_bf16_split(acc, a_lo + 2 * k, a_hi, b_lo + 2 * k, b_hi, idesc, first | (uint32_t)(t | k));
+                umma_bf16_split(acc + BLOCK_N, a_lo + h_step + 2 * k, a_hi, b_lo + 2 * k, b_hi, idesc,
+                                first | (uint32_t)(t | k));
+              }
+              b_lo += B_BYTES >> 4;
             }
-            if (!p.resident) umma_commit(&b_empty[bs]);
           }
           __syncwarp();
           first = 1;
-          if (!p.resident) {
-            if (++bs == p.nb) { bs = 0; bph ^= 1; }
-          } else {
-            b_lo += B_BYTES >> 4;
+        } else {
+          // one elected lane waits on the weight ring and issues; bs / bph are recomputed by every lane afterwards
+          if (elect_one()) {
+            int bs_l = bs;
+            uint32_t bph_l = bph;
+            for (int t = 0; t < p.n_taps; ++t) {
+              mbar_wait(&b_full[bs_l], bph_l);
+              tc_fence_after();
+              const uint32_t b_lo_t = desc_lo(smem_u32(sB + bs_l * B_BYTES), 16);
+              const uint32_t a_lo = a_lo0 + (uint32_t)p.taps[t].row_off16;
+#pragma unroll
+              for (int k = 0; k < CIN_BLK / 16; ++k) {
+                umma_bf16_split(acc, a_lo + 2 * k, a_hi, b_lo_t + 2 * k, b_hi, idesc, first | (uint32_t)(t | k));
+                umma_bf16_split(acc + BLOCK_N, a_lo + h_step + 2 * k, a_hi, b_lo_t + 2 * k, b_hi, idesc,
+                                first | (uint32_t)(t | k));
+              }
+              umma_commit(&b_empty[bs_l]);
+              if (++bs_l == p.nb) { bs_l = 0; bph_l ^= 1; }
+            }
           }
+          __syncwarp();
+          first = 1;
+          for (int t = 0; t < p.n_taps; ++t)
+            if (++bs == p.nb) { bs = 0; bph ^= 1; }
         }
         if (elect_one()) umma_commit(&a_empty[ab]);
         __syncwarp();

@@ -99,42 +99,41 @@ __global__ void __launch_bounds__(192)
 
   if (warp == 0) {
     // ===== TMA producer (warp-uniform loop, one elected lane issues: keeps TMA operands in uniform registers) =====
-    int stage = 0;
-    uint32_t phase = 0;
-    for (int kb = 0; kb < num_kb; ++kb) {
-      const int tap = kb / p.c_chunks, cc = kb - tap * p.c_chunks;
-      mbar_wait(&empty_bar[stage], phase ^ 1);
-      if (elect_one()) {
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int tap = kb / p.c_chunks, cc = kb - tap * p.c_chunks;
+        mbar_wait(&empty_bar[stage], phase ^ 1);
         mbar_arrive_expect_tx(&full_bar[stage], Cfg::STAGE_BYTES);
         uint8_t* sa = smem + stage * Cfg::STAGE_BYTES;
         tma_load_4d(sa, &map_a, &full_bar[stage], cc * CIN_BLK, ox0 * p.in_mul + p.taps[tap].dw,
                     oy0 * p.in_mul + p.taps[tap].dh, n_img);
         tma_load_2d(sa + Cfg::A_BYTES, &map_b, &full_bar[stage], p.taps[tap].wk + cc * CIN_BLK, n0);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
-      __syncwarp();
-      if (++stage == STAGES) { stage = 0; phase ^= 1; }
     }
+    __syncwarp();
   } else if (warp == 1) {
     // ===== MMA issuer =====
     constexpr uint32_t idesc = umma_idesc_bf16(128, BLOCK_N, 0, 0);
     const uint32_t d_hi = desc_hi(8 * ROW_BYTES, ROW_BYTES);      // same geometry for A and B tiles
-    int stage = 0;
-    uint32_t phase = 0;
-    for (int kb = 0; kb < num_kb; ++kb) {
-      mbar_wait(&full_bar[stage], phase);
-      tc_fence_after();
-      const uint32_t sa = smem_u32(smem + stage * Cfg::STAGE_BYTES);
-      const uint32_t a_lo = desc_lo(sa, 16), b_lo = desc_lo(sa + Cfg::A_BYTES, 16);
-      if (elect_one()) {
+    if (elect_one()) {                                            // one lane waits and issues for the whole tile
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t sa = smem_u32(smem + stage * Cfg::STAGE_BYTES);
+        const uint32_t a_lo = desc_lo(sa, 16), b_lo = desc_lo(sa + Cfg::A_BYTES, 16);
 #pragma unroll
         for (int k = 0; k < CIN_BLK / 16; ++k)
           umma_bf16_split(tmem_base, a_lo + 2 * k, d_hi, b_lo + 2 * k, d_hi, idesc, (uint32_t)(kb | k));
         umma_commit(&empty_bar[stage]);  // frees this stage once the MMAs above have read it
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
       }
-      __syncwarp();
-      if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      umma_commit(&tmem_full_bar);
     }
-    if (elect_one()) umma_commit(&tmem_full_bar);
     __syncwarp();
   } else if (warp >= 2) {
     // ===== epilogue =====

@@ -84,15 +84,15 @@ __global__ void __launch_bounds__(192, 1)
 
   if (warp == 0) {
     // ===== TMA producer: x halo (all channel chunks) + dy block per stage =====
-    int stage = 0;
-    uint32_t phase = 0;
-    const uint32_t tx_bytes = (uint32_t)(p.n_chunks * p.HHx * p.HWx * rbx + p.b_boxes * dy_box);
-    for (int t = t_beg; t < t_end; ++t) {
-      const int n = t / (p.blocks_w * p.blocks_h);
-      const int r = t - n * (p.blocks_w * p.blocks_h);
-      const int oy0 = (r / p.blocks_w) * kWhRows, ox0 = (r % p.blocks_w) * kWhCols;
-      mbar_wait(&empty_bar[stage], phase ^ 1);
-      if (elect_one()) {
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      const uint32_t tx_bytes = (uint32_t)(p.n_chunks * p.HHx * p.HWx * rbx + p.b_boxes * dy_box);
+      for (int t = t_beg; t < t_end; ++t) {
+        const int n = t / (p.blocks_w * p.blocks_h);
+        const int r = t - n * (p.blocks_w * p.blocks_h);
+        const int oy0 = (r / p.blocks_w) * kWhRows, ox0 = (r % p.blocks_w) * kWhCols;
+        mbar_wait(&empty_bar[stage], phase ^ 1);
         mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
         uint8_t* sx = smem + stage * p.stage_bytes;
         for (int c = 0; c < p.n_chunks; ++c)
@@ -100,26 +100,26 @@ __global__ void __launch_bounds__(192, 1)
         uint8_t* sy = sx + x_total;
         for (int b = 0; b < p.b_boxes; ++b)
           tma_load_4d(sy + b * dy_box, &map_dy, &full_bar[stage], co0 + b * p.co_blk, ox0, oy0, n);
+        if (++stage == p.stages) { stage = 0; phase ^= 1; }
       }
-      __syncwarp();
-      if (++stage == p.stages) { stage = 0; phase ^= 1; }
     }
+    __syncwarp();
   } else if (warp == 1) {
-    // ===== MMA issuer =====
+    // ===== MMA issuer: one elected lane waits and issues =====
     const uint32_t idesc = umma_idesc_bf16(128, p.n_cols, 1, 1);
     const uint32_t a_hi = desc_hi(8 * rbx, rbx), b_hi = desc_hi(8 * rby, rby);
     const uint32_t a_ystep = (uint32_t)(p.HWx * rbx) >> 4;          // next block row: one halo line down
     const uint32_t b_ystep = (uint32_t)(kWhCols * rby) >> 4;        // next block row: 16 dy rows down
     const uint32_t b_lbo = ((uint32_t)dy_box >> 4) << 16;
-    int stage = 0;
-    uint32_t phase = 0, first = 0;
-    for (int t = t_beg; t < t_end; ++t) {
-      mbar_wait(&full_bar[stage], phase);
-      tc_fence_after();
-      const uint32_t sx = smem_u32(smem + stage * p.stage_bytes);
-      const uint32_t x_lo = (sx >> 4) & 0x3FFF;
-      const uint32_t y_lo = (((sx + x_total) >> 4) & 0x3FFF) | b_lbo;
-      if (elect_one()) {
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0, first = 0;
+      for (int t = t_beg; t < t_end; ++t) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t sx = smem_u32(smem + stage * p.stage_bytes);
+        const uint32_t x_lo = (sx >> 4) & 0x3FFF;
+        const uint32_t y_lo = (((sx + x_total) >> 4) & 0x3FFF) | b_lbo;
         for (int m = 0; m < my_mt; ++m) {
           const uint32_t a_lo = x_lo + p.tiles[mt0 + m].lo_const;
           const uint32_t acc = tmem_base + m * p.n_cols;
@@ -128,12 +128,11 @@ __global__ void __launch_bounds__(192, 1)
             umma_bf16_split(acc, a_lo + y * a_ystep, a_hi, y_lo + y * b_ystep, b_hi, idesc, first | (uint32_t)y);
         }
         umma_commit(&empty_bar[stage]);
+        first = 1;
+        if (++stage == p.stages) { stage = 0; phase ^= 1; }
       }
-      __syncwarp();
-      first = 1;
-      if (++stage == p.stages) { stage = 0; phase ^= 1; }
+      umma_commit(&tmem_full_bar);
     }
-    if (elect_one()) umma_commit(&tmem_full_bar);
     __syncwarp();
   } else if (warp >= 2 && t_end > t_beg) {
     // ===== epilogue: TMEM -> red.global.add.f32x4 =====

@@ -82,15 +82,15 @@ __global__ void __launch_bounds__(192)
 
   if (warp == 0) {
     // ===== TMA producer =====
-    int stage = 0;
-    uint32_t phase = 0;
-    const uint32_t tx_bytes = (uint32_t)(b_bytes + my_mt * a_tile_bytes);
-    for (int t = t_beg; t < t_end; ++t) {
-      const int n = t / (p.tiles_w * p.tiles_h);
-      const int r = t - n * (p.tiles_w * p.tiles_h);
-      const int oy0 = (r / p.tiles_w) * p.th, ox0 = (r % p.tiles_w) * p.tw;
-      mbar_wait(&empty_bar[stage], phase ^ 1);
-      if (elect_one()) {
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      const uint32_t tx_bytes = (uint32_t)(b_bytes + my_mt * a_tile_bytes);
+      for (int t = t_beg; t < t_end; ++t) {
+        const int n = t / (p.tiles_w * p.tiles_h);
+        const int r = t - n * (p.tiles_w * p.tiles_h);
+        const int oy0 = (r / p.tiles_w) * p.th, ox0 = (r % p.tiles_w) * p.tw;
+        mbar_wait(&empty_bar[stage], phase ^ 1);
         mbar_arrive_expect_tx(&full_bar[stage], tx_bytes);
         uint8_t* sb = smem + stage * stage_bytes;
         for (int b = 0; b < p.b_boxes; ++b)
@@ -102,39 +102,38 @@ __global__ void __launch_bounds__(192)
             tma_load_4d(sa + m * a_tile_bytes + b * a_box_bytes, &map_x, &full_bar[stage], s.c0,
                         ox0 * p.in_mul + s.dw, oy0 * p.in_mul + s.dh, n);
           }
+        if (++stage == p.stages) { stage = 0; phase ^= 1; }
       }
-      __syncwarp();
-      if (++stage == p.stages) { stage = 0; phase ^= 1; }
     }
+    __syncwarp();
   } else if (warp == 1) {
-    // ===== MMA issuer =====
+    // ===== MMA issuer: one elected lane waits and issues =====
     const uint32_t idesc = umma_idesc_bf16(128, p.n_cols, 1, 1);
     const uint32_t a_hi = desc_hi(8 * a_row_bytes, a_row_bytes), b_hi = desc_hi(8 * b_row_bytes, b_row_bytes);
     const uint32_t a_kstep = (uint32_t)(16 * a_row_bytes) >> 4, b_kstep = (uint32_t)(16 * b_row_bytes) >> 4;
     const uint32_t a_tstep = (uint32_t)a_tile_bytes >> 4;
     const int ksteps = p.pix / 16;
-    int stage = 0;
-    uint32_t phase = 0;
-    uint32_t first = 0;
-    for (int t = t_beg; t < t_end; ++t) {
-      mbar_wait(&full_bar[stage], phase);
-      tc_fence_after();
-      const uint32_t sb = smem_u32(smem + stage * stage_bytes);
-      const uint32_t b_lo0 = desc_lo(sb, (uint32_t)b_box_bytes);
-      uint32_t a_lo = desc_lo(sb + b_bytes, (uint32_t)a_box_bytes);
-      if (elect_one()) {
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      uint32_t first = 0;
+      for (int t = t_beg; t < t_end; ++t) {
+        mbar_wait(&full_bar[stage], phase);
+        tc_fence_after();
+        const uint32_t sb = smem_u32(smem + stage * stage_bytes);
+        const uint32_t b_lo0 = desc_lo(sb, (uint32_t)b_box_bytes);
+        uint32_t a_lo = desc_lo(sb + b_bytes, (uint32_t)a_box_bytes);
         for (int m = 0; m < my_mt; ++m, a_lo += a_tstep) {
           const uint32_t acc = tmem_base + m * p.n_cols;
           for (int ks = 0; ks < ksteps; ++ks)
             umma_bf16_split(acc, a_lo + ks * a_kstep, a_hi, b_lo0 + ks * b_kstep, b_hi, idesc, first | (uint32_t)ks);
         }
         umma_commit(&empty_bar[stage]);
+        first = 1;
+        if (++stage == p.stages) { stage = 0; phase ^= 1; }
       }
-      __syncwarp();
-      first = 1;
-      if (++stage == p.stages) { stage = 0; phase ^= 1; }
+      umma_commit(&tmem_full_bar);
     }
-    if (elect_one()) umma_commit(&tmem_full_bar);
     __syncwarp();
   } else if (warp >= 2 && t_end > t_beg) {
     // ===== epilogue: TMEM -> red.global.add.f32x4 =====
