@@ -294,9 +294,11 @@ int run_halo_problem(const void* a_src, int N, int Hs, int Ws, int Ck, const voi
   p.resident = (p.n_tiles == 1 && bank_tiles * b_bytes <= budget && bank_tiles * b_bytes <= 112 * 1024) ? 1 : 0;
   if (!force) {
     // Measured on B200 (tools/bench_convs.py): with streamed weights this kernel beats the per-tap kernel only
-    // where the output tile is narrow (Cn <= 64); with resident weights it always does.
+    // where the output tile is narrow (Cn <= 64) or a single 128-wide tile reads at most two channel chunks
+    // (residual 128->128: 33.0 vs 35.6 us, its dgrad 38.8 vs 41.8; deconv3 dgrad 62.8 vs 77.9); D's 256->512
+    // layers lose (140 vs 118 us).  With resident weights it always wins.
     const int64_t blocks = (int64_t)((Wv + 7) / 8) * ((Hv + 31) / 32) * N;
-    if (!p.resident && Cn > 64) return -2;
+    if (!p.resident && Cn > 64 && !(p.n_tiles == 1 && p.c_chunks <= 2)) return -2;
     if (blocks * 256 > 2 * (int64_t)N * Hv * Wv) return -2;    // small maps: too many padded pixels per 32x8 block
   }
   int nb;
