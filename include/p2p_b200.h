@@ -199,6 +199,11 @@ int p2p_tv_bwd_add(const float* x, const float* gscale, float* g, int B, int C, 
 /* ---- optimiser: torch.optim.Adam as used at train.py:241-242,386,390 (no weight decay, no amsgrad) */
 int p2p_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
                   float eps, int step, float grad_scale, void* stream);
+/* Same update with the step count (>= 1, already incremented) read from DEVICE memory, so that the launch can
+ * be replayed from a CUDA graph while the count advances (torch.optim.Adam's capturable=True mode,
+ * torch/optim/adam.py).  Bias corrections are computed on the device in double precision. */
+int p2p_adam_step_dev(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
+                      float eps, const int* step_dev, float grad_scale, void* stream);
 
 #ifdef __cplusplus
 }

@@ -68,6 +68,7 @@ SIGNATURES = {
     "p2p_tv_fwd": [_vp, _vp, _i, _i, _i, _i, _vp],
     "p2p_tv_bwd_add": [_vp, _vp, _vp, _i, _i, _i, _i, _vp],
     "p2p_adam_step": [_vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _i, _f, _vp],
+    "p2p_adam_step_dev": [_vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _vp, _f, _vp],
 }
 NOARG = {"p2p_version": C.c_int, "p2p_last_error": C.c_char_p, "p2p_device_supports_tc": C.c_int,
          "p2p_launch_count": C.c_longlong}

@@ -116,7 +116,15 @@ __global__ void tv_bwd_add_kernel(const float* __restrict__ x, const float* __re
 // p -= (lr / (1-b1^t)) * m / (sqrt(v)/sqrt(1-b2^t) + eps).  28 bytes per parameter (read p,g,m,v; write p,m,v).
 __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                                                    float* __restrict__ v, int64_t n4, int64_t n, float b1, float b2,
-                                                   float step_size, float inv_sqrt_bc2, float eps, float gs) {
+                                                   float step_size, float inv_sqrt_bc2, float eps, float gs,
+                                                   const int* __restrict__ step_dev) {
+  if (step_dev != nullptr) {
+    // step count lives in device memory (the launch is replayed from a CUDA graph): same double-precision bias
+    // corrections as the host path; step_size arrives holding lr
+    const int step = *step_dev;
+    step_size = (float)((double)step_size / (1.0 - pow((double)b1, (double)step)));
+    inv_sqrt_bc2 = (float)(1.0 / sqrt(1.0 - pow((double)b2, (double)step)));
+  }
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
     float4 P = reinterpret_cast<float4*>(p)[i];
@@ -239,7 +247,22 @@ int p2p_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float
   if (blocks < 1) blocks = 1;
   if (blocks > kSMs * 16) blocks = kSMs * 16;
   adam_kernel<<<(int)blocks, 256, 0, as_stream(stream)>>>(p, g, m, v, n4, n, beta1, beta2, step_size, inv_sqrt_bc2, eps,
-                                                         grad_scale);
+                                                         grad_scale, nullptr);
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_adam_step_dev(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
+                      float eps, const int* step_dev, float grad_scale, void* stream) {
+  P2P_REQUIRE(p && g && m && v && n > 0 && step_dev, "bad arguments");
+  P2P_REQUIRE(((uintptr_t)p % 16 == 0) && ((uintptr_t)g % 16 == 0) && ((uintptr_t)m % 16 == 0) &&
+                  ((uintptr_t)v % 16 == 0),
+              "buffers must be 16-byte aligned");
+  const int64_t n4 = n / 4;
+  int64_t blocks = (n4 + 255) / 256;
+  if (blocks < 1) blocks = 1;
+  if (blocks > kSMs * 16) blocks = kSMs * 16;
+  adam_kernel<<<(int)blocks, 256, 0, as_stream(stream)>>>(p, g, m, v, n4, n, beta1, beta2, lr, 1.f, eps, grad_scale,
+                                                         step_dev);
   P2P_LAUNCH_CHECK();
 }
 

@@ -48,8 +48,25 @@ class FusedAdam(torch.optim.Optimizer):
                 view.copy_(p.data)
                 p.data = view
                 p.grad = self.flat_g[off:off + k].view(p.shape)
-        self.steps = 0
+        self._steps = 0
+        self._step_t = None     # device-side step count (capturable mode)
         self.grad_scale = 1.0   # set to 1/world_size by the data-parallel trainer (all-reduce is a sum)
+
+    @property
+    def steps(self) -> int:
+        return int(self._step_t.item()) if self._step_t is not None else self._steps
+
+    @steps.setter
+    def steps(self, n: int):
+        self._steps = int(n)
+        if self._step_t is not None:
+            self._step_t.fill_(int(n))
+
+    def make_capturable(self):
+        """Keep the step count in device memory (torch.optim.Adam's capturable=True): `step()` then makes no
+        host-dependent launch and can be recorded into, and replayed from, a CUDA graph."""
+        if self._step_t is None:
+            self._step_t = torch.full((1,), self._steps, dtype=torch.int32, device=self.flat_p.device)
 
     def _rebind_grads(self):
         """Make sure every p.grad is still the flat view (a caller may have used set_to_none or assigned one)."""
@@ -76,9 +93,15 @@ class FusedAdam(torch.optim.Optimizer):
             raise NotImplementedError("closures are not supported")
         self._rebind_grads()
         g = self.param_groups[0]
-        self.steps += 1
+        if self._step_t is not None:
+            self._step_t.add_(1)
+            call("p2p_adam_step_dev", ptr(self.flat_p), ptr(self.flat_g), ptr(self.exp_avg), ptr(self.exp_avg_sq),
+                 self.numel, float(g["lr"]), float(g["betas"][0]), float(g["betas"][1]), float(g["eps"]),
+                 ptr(self._step_t), float(self.grad_scale))
+            return
+        self._steps += 1
         call("p2p_adam_step", ptr(self.flat_p), ptr(self.flat_g), ptr(self.exp_avg), ptr(self.exp_avg_sq), self.numel,
-             float(g["lr"]), float(g["betas"][0]), float(g["betas"][1]), float(g["eps"]), self.steps,
+             float(g["lr"]), float(g["betas"][0]), float(g["betas"][1]), float(g["eps"]), self._steps,
              float(self.grad_scale))
 
     def state_dict(self):

@@ -53,8 +53,17 @@ class Pix2PixTrainer:
     """optimizer_g / optimizer_d loop of train.py:241-242, :294-390."""
 
     def __init__(self, net_g, net_d, lr: float = 2e-4, beta1: float = 0.5, process_group=None,
-                 bucket_bytes: int = 8 << 20):
+                 bucket_bytes: int = 8 << 20, cuda_graph: bool = False, graph_warmup: int = 2):
         self.net_g, self.net_d = net_g, net_d
+        # cuda_graph=True: the first `graph_warmup` calls of step() run eagerly, the next one records the whole
+        # iteration (~650 launches, both backward passes, the all-reduces and both Adam updates) into one CUDA
+        # graph per input shape, and every later call is three input copies and one graph launch.  The host
+        # needs ~10 ms to enqueue an iteration kernel by kernel, which bounds small batches; a replay needs
+        # well under 1 ms.  The returned tensors are then the graph's own output buffers: each call overwrites
+        # the values returned by the previous one (clone what must be kept).
+        self.cuda_graph, self.graph_warmup = bool(cuda_graph), int(graph_warmup)
+        self._graphs, self._eager_calls = {}, 0
+        self.graph_launches = 0          # kernels of libp2p_b200.so recorded in the last captured graph
         self.optimizer_g = FusedAdam(net_g.parameters(), lr=lr, betas=(beta1, 0.999))
         self.optimizer_d = FusedAdam([p for p in net_d.parameters() if p.requires_grad], lr=lr, betas=(beta1, 0.999))
         self.red_g = GradReducer(process_group, bucket_bytes)
@@ -62,6 +71,9 @@ class Pix2PixTrainer:
         self.world = self.red_g.world
         self.optimizer_g.grad_scale = self.optimizer_d.grad_scale = 1.0 / self.world
         self._c_reals = [c[1] for c in net_d._cfg]
+        if self.cuda_graph:
+            self.optimizer_g.make_capturable()
+            self.optimizer_d.make_capturable()
 
     def broadcast_parameters(self, src: int = 0):
         """identical replicas at start (rank `src` wins), including BatchNorm buffers and SN u/v"""
@@ -78,6 +90,38 @@ class Pix2PixTrainer:
                     dist.broadcast(p.data, src)
 
     def step(self, real_a: torch.Tensor, real_b: torch.Tensor, g_input: torch.Tensor) -> Dict[str, torch.Tensor]:
+        if not self.cuda_graph:
+            return self._step_eager(real_a, real_b, g_input)
+        key = (tuple(real_a.shape), tuple(real_b.shape), tuple(g_input.shape), E.get_precision())
+        rec = self._graphs.get(key)
+        if rec is None:
+            if self._eager_calls < self.graph_warmup:
+                # lazily created workspaces, kernel attributes and NCCL communicators come to life here
+                self._eager_calls += 1
+                return self._step_eager(real_a.cuda(non_blocking=True), real_b.cuda(non_blocking=True),
+                                        g_input.cuda(non_blocking=True))
+            rec = self._capture(real_a, real_b, g_input)
+            self._graphs[key] = rec
+        for dst, src in zip(rec["inputs"], (real_a, real_b, g_input)):
+            dst.copy_(src, non_blocking=True)
+        rec["graph"].replay()
+        return rec["outputs"]
+
+    def _capture(self, real_a, real_b, g_input):
+        from . import _lib as L
+        dev = self.optimizer_g.flat_p.device
+        inputs = [torch.empty(t.shape, dtype=torch.float32, device=dev) for t in (real_a, real_b, g_input)]
+        for dst, src in zip(inputs, (real_a, real_b, g_input)):
+            dst.copy_(src, non_blocking=True)
+        graph = torch.cuda.CUDAGraph()
+        torch.cuda.synchronize()
+        before = L.launch_count()
+        with torch.cuda.graph(graph):
+            outputs = self._step_eager(*inputs)
+        self.graph_launches = L.launch_count() - before
+        return {"graph": graph, "inputs": inputs, "outputs": outputs}
+
+    def _step_eager(self, real_a: torch.Tensor, real_b: torch.Tensor, g_input: torch.Tensor) -> Dict[str, torch.Tensor]:
         net_g, net_d, cr = self.net_g, self.net_d, self._c_reals
         last = lambda maps: [s[-1] for s in maps]                                         # noqa: E731
         ones = [1] * 3

@@ -1,0 +1,100 @@
+"""CUDA-graph replay of the training iteration (Pix2PixTrainer(cuda_graph=True)) against the same iteration
+launched kernel by kernel, and the device-step Adam entry point against the host-step one.
+
+Trajectories cannot be compared: two EAGER runs from the same weights already drift apart (fp32 mode: losses
+1e-4, generator output 0.25 max after seven iterations at batch 2, 32x32 -- tools/graph_vs_eager.py) because
+the float atomics of the split-K weight gradients land in a different order each run and Adam's g/sqrt(v)
+amplifies that.  So every iteration is compared from the SAME state: before each step the eager twin loads the
+graphed trainer's weights, buffers and optimizer state, both take one step on the same batch, and outputs,
+gradients and moments must agree to the single-step noise level."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import pix2pix_oracle as orc
+
+DEV = "cuda"
+
+
+@pytest.fixture(autouse=True)
+def _restore_precision():
+    yield
+    import p2p_pytorch_b200 as P
+    P.set_precision("bf16")
+
+
+def _nets(P):
+    g = P.ExpandNetwork().to(DEV)
+    d = P.MultiscaleDiscriminator(6, 64, getIntermFeat=True).to(DEV)
+    g.load_state_dict(orc.init_g_state(123))
+    d.load_state_dict(orc.init_d_state(124))
+    return g, d
+
+
+def _rms_rel(a, b):
+    a, b = a.double(), b.double()
+    return ((a - b).pow(2).mean().sqrt() / b.pow(2).mean().sqrt().clamp_min(1e-30)).item()
+
+
+@pytest.mark.parametrize("precision,tol_out,tol_grad", [("fp32", 1e-5, 1e-3), ("bf16", 1e-2, 5e-2)])
+def test_graph_replay_matches_eager_step_by_step(precision, tol_out, tol_grad):
+    import p2p_pytorch_b200 as P
+    P.set_precision(precision)
+    g1, d1 = _nets(P)
+    g2, d2 = _nets(P)
+    tr_graph = P.Pix2PixTrainer(g1, d1, cuda_graph=True, graph_warmup=1)
+    tr_eager = P.Pix2PixTrainer(g2, d2)
+    for it in range(6):
+        g2.load_state_dict(g1.state_dict())
+        d2.load_state_dict(d1.state_dict())
+        tr_eager.optimizer_g.load_state_dict(tr_graph.optimizer_g.state_dict())
+        tr_eager.optimizer_d.load_state_dict(tr_graph.optimizer_d.state_dict())
+        a, b, c = orc.synthetic_batch(2, 32, 32, 50 + it)
+        dev_in = [t.to(DEV) for t in (a, b, c)]
+        # host tensors are legal inputs of the graphed step (copied into the graph's input buffers)
+        graph_in = [t.pin_memory() for t in (a, b, c)] if it % 2 else dev_in
+        out_g = {k: v.detach().float().clone() for k, v in tr_graph.step(*graph_in).items()}
+        out_e = {k: v.detach().float() for k, v in tr_eager.step(*dev_in).items()}
+        for k in ("loss_d", "loss_g", "loss_feat", "loss_tv", "loss_g_gan"):
+            assert abs(out_g[k].item() - out_e[k].item()) <= tol_out * abs(out_e[k].item()), (it, k)
+        assert (out_g["fake_b"] - out_e["fake_b"]).abs().max().item() <= tol_out, it
+        for og, oe in ((tr_graph.optimizer_g, tr_eager.optimizer_g), (tr_graph.optimizer_d, tr_eager.optimizer_d)):
+            assert _rms_rel(og.flat_g, oe.flat_g) <= tol_grad, (it, _rms_rel(og.flat_g, oe.flat_g))
+            assert _rms_rel(og.exp_avg, oe.exp_avg) <= tol_grad, it
+            assert _rms_rel(og.exp_avg_sq, oe.exp_avg_sq) <= 2 * tol_grad, it
+            assert og.steps == oe.steps == it + 1
+        for (n, b1), (_, b2) in zip(list(g1.named_buffers()) + list(d1.named_buffers()),
+                                    list(g2.named_buffers()) + list(d2.named_buffers())):
+            assert torch.allclose(b1.float(), b2.float(), rtol=20 * tol_out, atol=20 * tol_out), (it, n)
+    assert len(tr_graph._graphs) == 1 and tr_graph.graph_launches > 100
+
+
+def test_graph_recaptures_per_shape():
+    import p2p_pytorch_b200 as P
+    g, d = _nets(P)
+    tr = P.Pix2PixTrainer(g, d, cuda_graph=True, graph_warmup=1)
+    for it, (bsz, h, w) in enumerate([(2, 32, 32), (2, 32, 32), (1, 64, 48), (2, 32, 32), (1, 64, 48)]):
+        a, b, c = orc.synthetic_batch(bsz, h, w, it)
+        out = tr.step(a.to(DEV), b.to(DEV), c.to(DEV))
+        assert out["fake_b"].shape == (bsz, 3, h, w)
+        assert torch.isfinite(out["loss_g"]).item() and torch.isfinite(out["loss_d"]).item()
+    assert len(tr._graphs) == 2 and tr.optimizer_g.steps == 5
+
+
+def test_adam_device_step_matches_host_step():
+    from p2p_pytorch_b200._lib import call, ptr
+    gen = torch.Generator(device=DEV).manual_seed(5)
+    n = 100_003 // 4 * 4 + 4
+    p0 = torch.randn(n, device=DEV, generator=gen)
+    state = [[p0.clone(), torch.zeros(n, device=DEV), torch.zeros(n, device=DEV)] for _ in range(2)]
+    step_t = torch.zeros(1, dtype=torch.int32, device=DEV)
+    for step in range(1, 8):
+        grad = torch.randn(n, device=DEV, generator=gen)
+        p, m, v = state[0]
+        call("p2p_adam_step", ptr(p), ptr(grad), ptr(m), ptr(v), n, 2e-4, 0.5, 0.999, 1e-8, step, 0.5)
+        p, m, v = state[1]
+        step_t.add_(1)
+        call("p2p_adam_step_dev", ptr(p), ptr(grad), ptr(m), ptr(v), n, 2e-4, 0.5, 0.999, 1e-8, ptr(step_t), 0.5)
+    for x, y in zip(*state):
+        assert torch.allclose(x, y, rtol=1e-6, atol=1e-9)
