@@ -25,6 +25,7 @@ sys.path.insert(0, ROOT)
 
 import torch  # noqa: E402
 
+RES_CONV_DRAM_BYTES = None          # dram bytes of one residual-conv launch from ncu --set full (profiles/); None until re-captured
 FLOP_PER_IMG_256 = 173.41e9          # necessary conv FLOPs of one training step per image
 METRIC = "pix2pix 256x256 train images/sec"
 
@@ -259,8 +260,8 @@ def run_ours(args, rank, world, local_rank):
                             "frac": ach / tf_burst,
                             # dram__bytes_read.sum + dram__bytes_write.sum of this launch, ncu --set full
                             # (profiles/r01c_ncu_dominant_kernels.md); valid for the default B=16, 256x256 shape only
-                            "traffic": 18.16e6 if (B == 16 and S == 256) else None, "peak_source": which,
-                            "kernel": "conv_tc_kernel<128,64> (3x3 128->128 residual conv fwd, bf16, fp32 accumulate)",
+                            "traffic": RES_CONV_DRAM_BYTES if (B == 16 and S == 256) else None, "peak_source": which,
+                            "kernel": "conv_halo_swap_kernel<64> (3x3 128->128 residual conv fwd, bf16, fp32 accumulate)",
                             "ms_per_launch": kms}
     except Exception as e:                                   # e.g. fp32 verification mode: no tensor-core kernel
         line["roofline"] = {"bound": "tensor", "achieved": None, "peak": tf_burst, "unit": "TFLOP/s", "frac": None,
