@@ -91,6 +91,28 @@ int p2p_unpack_wgrad(const float* dw_acc, float* grad, const float* w, const flo
  * u, v are read when this runs -- quirk Q1 of SURVEY.md section 8a). */
 int p2p_sn_weight_grad(float* grad_wbar, const float* dot, const float* sigma, const float* u, const float* v, int rows,
                        int cols, void* stream);
+
+/* Batched forms of the three calls above: one launch for all layers of a network (the per-layer launches are
+ * 5-9 us each and there are ~140 of them per training iteration).  `jobs` is a HOST array of n descriptors with
+ * the argument meaning of the single-layer call; it is copied into the launch parameters.  n <= P2P_MULTI_MAX
+ * per call.  They have no counterpart of their own in the reference: each job is the same weight preparation /
+ * gradient un-packing the reference's conv layers do inside cuDNN. */
+#define P2P_MULTI_MAX 24
+typedef struct p2p_pack_job {
+  const float* w; const float* sigma; void* w_packed; void* wt_packed;
+  int32_t co_real, ci_real, Co, Ci, kh, kw;
+} p2p_pack_job;
+typedef struct p2p_unpack_job {
+  const float* dw_acc; float* grad; const float* w; const float* sigma; float* dot;
+  int32_t co_real, ci_real, Co, Ci, kh, kw;
+} p2p_unpack_job;
+typedef struct p2p_sn_grad_job {
+  float* grad_wbar; const float* dot; const float* sigma; const float* u; const float* v;
+  int32_t rows, cols;
+} p2p_sn_grad_job;
+int p2p_pack_weights_multi(int n, const p2p_pack_job* jobs, int dtype, void* stream);
+int p2p_unpack_wgrad_multi(int n, const p2p_unpack_job* jobs, void* stream);
+int p2p_sn_weight_grad_multi(int n, const p2p_sn_grad_job* jobs, void* stream);
 /* One power iteration for `n_layers` weight matrices at once (networks.py:537-547):
  * v = l2n(W^T u); u = l2n(W v); sigma = u . (W v).  Arrays of device pointers live in HOST memory
  * (they are kernel arguments).  tmp: device scratch of at least sum(rows+cols) floats. */

@@ -25,6 +25,35 @@ class Conv(C.Structure):
                 ("N", "Hi", "Wi", "Ci", "Ho", "Wo", "Co", "kh", "kw", "stride", "pad", "co_real", "ci_real", "act")]
 
 
+MULTI_MAX = 24   # P2P_MULTI_MAX
+
+
+class PackJob(C.Structure):
+    """struct p2p_pack_job"""
+    _fields_ = [("w", C.c_void_p), ("sigma", C.c_void_p), ("w_packed", C.c_void_p), ("wt_packed", C.c_void_p)] + \
+               [(n, C.c_int32) for n in ("co_real", "ci_real", "Co", "Ci", "kh", "kw")]
+
+
+class UnpackJob(C.Structure):
+    """struct p2p_unpack_job"""
+    _fields_ = [("dw_acc", C.c_void_p), ("grad", C.c_void_p), ("w", C.c_void_p), ("sigma", C.c_void_p),
+                ("dot", C.c_void_p)] + [(n, C.c_int32) for n in ("co_real", "ci_real", "Co", "Ci", "kh", "kw")]
+
+
+class SnGradJob(C.Structure):
+    """struct p2p_sn_grad_job"""
+    _fields_ = [("grad_wbar", C.c_void_p), ("dot", C.c_void_p), ("sigma", C.c_void_p), ("u", C.c_void_p),
+                ("v", C.c_void_p), ("rows", C.c_int32), ("cols", C.c_int32)]
+
+
+def call_multi(name: str, jobs, *extra) -> None:
+    """Run a batched entry point over a list of job structures, P2P_MULTI_MAX per launch."""
+    for i in range(0, len(jobs), MULTI_MAX):
+        chunk = jobs[i:i + MULTI_MAX]
+        arr = (type(chunk[0]) * len(chunk))(*chunk)
+        call(name, len(chunk), C.cast(arr, C.c_void_p), *extra)
+
+
 class P2PError(RuntimeError):
     pass
 
@@ -67,6 +96,9 @@ SIGNATURES = {
     "p2p_l1_bwd": [_vp, _vp, _f, _vp, _vp, _i64, _i, _i, _i, _vp],
     "p2p_tv_fwd": [_vp, _vp, _i, _i, _i, _i, _vp],
     "p2p_tv_bwd_add": [_vp, _vp, _vp, _i, _i, _i, _i, _vp],
+    "p2p_pack_weights_multi": [_i, _vp, _i, _vp],
+    "p2p_unpack_wgrad_multi": [_i, _vp, _vp],
+    "p2p_sn_weight_grad_multi": [_i, _vp, _vp],
     "p2p_adam_step": [_vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _i, _f, _vp],
     "p2p_adam_step_dev": [_vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _vp, _f, _vp],
 }

@@ -358,8 +358,14 @@ __global__ void __launch_bounds__(256, 3)
 template <typename T>
 __global__ void __launch_bounds__(256)
     bn_bwd_apply_kernel(const T* __restrict__ dz, const T* __restrict__ r, const float* __restrict__ sb,
-                        const double* __restrict__ red, T* __restrict__ dr, float* __restrict__ dbias, int64_t pixels,
-                        int C, int c_real) {
+                        const double* __restrict__ red, T* __restrict__ dr, float* __restrict__ dbias,
+                        float* __restrict__ dgamma, float* __restrict__ dbeta, int64_t pixels, int C, int c_real) {
+  if (blockIdx.x == 0 && dgamma != nullptr && dbeta != nullptr) {      // d gamma = sum dz * xhat, d beta = sum dz
+    for (int c = threadIdx.x; c < c_real; c += blockDim.x) {
+      dbeta[c] += (float)red[c];
+      dgamma[c] += (float)red[C + c];
+    }
+  }
   const int C8 = C >> 3;
   const int c8 = threadIdx.x % C8, lane_p = threadIdx.x / C8, ppb = 256 / C8;
   float m1[8], m2[8], sc[8], mean[8], istd[8], sd[8];
@@ -397,14 +403,6 @@ __global__ void __launch_bounds__(256)
       for (int l = 0; l < ppb; ++l) acc += sh[c & 7][l * C8 + (c >> 3)];
       atomicAdd(dbias + c, acc);
     }
-  }
-}
-
-__global__ void bn_param_grad_kernel(const double* __restrict__ red, float* dgamma, float* dbeta, int C, int c_real) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c < c_real) {
-    dbeta[c] += (float)red[c];
-    dgamma[c] += (float)red[C + c];
   }
 }
 
@@ -743,11 +741,7 @@ int p2p_bn_bwd_apply(const void* dz, const void* r, const float* sb, const doubl
   P2P_REQUIRE(C % 16 == 0 && C <= 512, "C must be a multiple of 16, <= 512");
   const int ppb = 256 / (C / 8);
   P2P_DISPATCH(dtype, bn_bwd_apply_kernel<T><<<red_ew_grid(pixels, ppb), 256, 0, as_stream(stream)>>>(
-                          (const T*)dz, (const T*)r, sb, red, (T*)dr, dbias, pixels, C, c_real););
-  if (dgamma != nullptr && dbeta != nullptr) {
-    bn_param_grad_kernel<<<cdiv(C, 128), 128, 0, as_stream(stream)>>>(red, dgamma, dbeta, C, c_real);
-    count_launches(1);
-  }
+                          (const T*)dz, (const T*)r, sb, red, (T*)dr, dbias, dgamma, dbeta, pixels, C, c_real););
   P2P_LAUNCH_CHECK();
 }
 

@@ -69,6 +69,74 @@ __global__ void sn_weight_grad_kernel(float* __restrict__ grad, const float* __r
   }
 }
 
+// ---- batched forms: blockIdx.y = job, the blocks of a row stride over that job's elements -----------------
+struct PackTable { p2p_pack_job j[P2P_MULTI_MAX]; };
+struct UnpackTable { p2p_unpack_job j[P2P_MULTI_MAX]; };
+struct SnGradTable { p2p_sn_grad_job j[P2P_MULTI_MAX]; };
+
+template <typename T>
+__global__ void __launch_bounds__(256) pack_weights_multi_kernel(const __grid_constant__ PackTable tb) {
+  const p2p_pack_job& jb = tb.j[blockIdx.y];
+  const float* __restrict__ w = jb.w;
+  T* __restrict__ wp = static_cast<T*>(jb.w_packed);
+  T* __restrict__ wt = static_cast<T*>(jb.wt_packed);
+  const float inv = jb.sigma != nullptr ? 1.f / *jb.sigma : 1.f;
+  const uint32_t Ci = jb.Ci, Co = jb.Co, taps = jb.kh * jb.kw, ci_real = jb.ci_real, co_real = jb.co_real;
+  const uint32_t total = Co * taps * Ci;                       // < 2^31, checked by the caller
+  for (uint32_t i = blockIdx.x * 256 + threadIdx.x; i < total; i += gridDim.x * 256) {
+    if (wp != nullptr) {  // i enumerates [Co][tap][Ci]
+      const uint32_t ci = i % Ci, q = i / Ci;
+      const uint32_t tap = q % taps, co = q / taps;
+      const float v = (co < co_real && ci < ci_real) ? w[(co * ci_real + ci) * taps + tap] * inv : 0.f;
+      stf(wp + i, v);
+    }
+    if (wt != nullptr) {  // i enumerates [Ci][tap][Co]
+      const uint32_t co = i % Co, q = i / Co;
+      const uint32_t tap = q % taps, ci = q / taps;
+      const float v = (co < co_real && ci < ci_real) ? w[(co * ci_real + ci) * taps + tap] * inv : 0.f;
+      stf(wt + i, v);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) unpack_wgrad_multi_kernel(const __grid_constant__ UnpackTable tb) {
+  const p2p_unpack_job& jb = tb.j[blockIdx.y];
+  const float* __restrict__ acc = jb.dw_acc;
+  const float* __restrict__ w = jb.w;
+  float* __restrict__ grad = jb.grad;
+  const float scale = jb.sigma != nullptr ? 1.f / *jb.sigma : 1.f;
+  const uint32_t Ci = jb.Ci, Co = jb.Co, taps = jb.kh * jb.kw, ci_real = jb.ci_real;
+  const uint32_t total = (uint32_t)jb.co_real * ci_real * taps;
+  float d = 0.f;
+  for (uint32_t i = blockIdx.x * 256 + threadIdx.x; i < total; i += gridDim.x * 256) {
+    const uint32_t tap = i % taps, q = i / taps;
+    const uint32_t ci = q % ci_real, co = q / ci_real;
+    const float a = acc[(tap * Ci + ci) * Co + co];
+    grad[i] += a * scale;
+    if (jb.dot != nullptr) d += a * w[i];
+  }
+  if (jb.dot != nullptr) {                                    // uniform per block row
+    const float tot = block_sum<float>(d);
+    if (threadIdx.x == 0 && tot != 0.f) atomicAdd(jb.dot, tot);
+  }
+}
+
+__global__ void __launch_bounds__(256) sn_weight_grad_multi_kernel(const __grid_constant__ SnGradTable tb) {
+  const p2p_sn_grad_job& jb = tb.j[blockIdx.y];
+  const float s = *jb.sigma;
+  const float coef = *jb.dot / (s * s);
+  const uint32_t cols = jb.cols, total = (uint32_t)jb.rows * cols;
+  for (uint32_t i = blockIdx.x * 256 + threadIdx.x; i < total; i += gridDim.x * 256) {
+    const uint32_t k = i % cols, r = i / cols;
+    jb.grad_wbar[i] -= coef * jb.u[r] * jb.v[k];
+  }
+}
+
+static inline int multi_grid_x(int64_t max_total) {
+  int64_t x = (max_total + 256 * 8 - 1) / (256 * 8);
+  return (int)(x < 1 ? 1 : (x > 96 ? 96 : x));
+}
+
 // ---- batched power iteration ---------------------------------------------------------------------
 struct SnTable {
   const float* w[P2P_SN_MAX_LAYERS];
@@ -183,6 +251,56 @@ int p2p_sn_weight_grad(float* grad_wbar, const float* dot, const float* sigma, c
   int64_t blocks = (total + 255) / 256;
   if (blocks > kSMs * 8) blocks = kSMs * 8;
   sn_weight_grad_kernel<<<(int)blocks, 256, 0, as_stream(stream)>>>(grad_wbar, dot, sigma, u, v, rows, cols);
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_pack_weights_multi(int n, const p2p_pack_job* jobs, int dtype, void* stream) {
+  P2P_REQUIRE(jobs && n >= 1 && n <= P2P_MULTI_MAX, "1..24 jobs per call");
+  PackTable tb;
+  int64_t mx = 0;
+  for (int i = 0; i < n; ++i) {
+    const p2p_pack_job& j = jobs[i];
+    P2P_REQUIRE(j.w && (j.w_packed || j.wt_packed), "null pointer in a job");
+    P2P_REQUIRE(j.co_real <= j.Co && j.ci_real <= j.Ci && j.Co % 16 == 0 && j.Ci % 16 == 0, "bad channel counts");
+    const int64_t total = (int64_t)j.Co * j.kh * j.kw * j.Ci;
+    P2P_REQUIRE(total < (1LL << 31), "weight tensor too large");
+    mx = total > mx ? total : mx;
+    tb.j[i] = j;
+  }
+  P2P_DISPATCH(dtype, pack_weights_multi_kernel<T><<<dim3(multi_grid_x(mx), n), 256, 0, as_stream(stream)>>>(tb););
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_unpack_wgrad_multi(int n, const p2p_unpack_job* jobs, void* stream) {
+  P2P_REQUIRE(jobs && n >= 1 && n <= P2P_MULTI_MAX, "1..24 jobs per call");
+  UnpackTable tb;
+  int64_t mx = 0;
+  for (int i = 0; i < n; ++i) {
+    const p2p_unpack_job& j = jobs[i];
+    P2P_REQUIRE(j.dw_acc && j.grad, "null pointer in a job");
+    P2P_REQUIRE(j.dot == nullptr || j.w != nullptr, "dot needs the weights");
+    const int64_t total = (int64_t)j.Co * j.kh * j.kw * j.Ci;
+    P2P_REQUIRE(total < (1LL << 31), "weight tensor too large");
+    mx = total > mx ? total : mx;
+    tb.j[i] = j;
+  }
+  unpack_wgrad_multi_kernel<<<dim3(multi_grid_x(mx), n), 256, 0, as_stream(stream)>>>(tb);
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_sn_weight_grad_multi(int n, const p2p_sn_grad_job* jobs, void* stream) {
+  P2P_REQUIRE(jobs && n >= 1 && n <= P2P_MULTI_MAX, "1..24 jobs per call");
+  SnGradTable tb;
+  int64_t mx = 0;
+  for (int i = 0; i < n; ++i) {
+    const p2p_sn_grad_job& j = jobs[i];
+    P2P_REQUIRE(j.grad_wbar && j.dot && j.sigma && j.u && j.v && j.rows > 0 && j.cols > 0, "null pointer in a job");
+    const int64_t total = (int64_t)j.rows * j.cols;
+    P2P_REQUIRE(total < (1LL << 31), "weight tensor too large");
+    mx = total > mx ? total : mx;
+    tb.j[i] = j;
+  }
+  sn_weight_grad_multi_kernel<<<dim3(multi_grid_x(mx), n), 256, 0, as_stream(stream)>>>(tb);
   P2P_LAUNCH_CHECK();
 }
 

@@ -83,6 +83,14 @@ class ConvPlan:
         call("p2p_pack_weights", ptr(weight), ptr(sigma), ptr(self.wp), ptr(self.wt), self.cout_real, self.cin_real,
              self.Co, self.Ci, self.k, self.k, L.dtype_code(dt))
 
+    def pack_job(self, weight, sigma, dt, want_wt=True) -> L.PackJob:
+        """Allocate the packed buffers and describe the packing for one batched p2p_pack_weights_multi launch."""
+        dev = weight.device
+        self.wp = _empty((self.Co, self.k, self.k, self.Ci), dt, dev)
+        self.wt = _empty((self.Ci, self.k, self.k, self.Co), dt, dev) if want_wt else None
+        return L.PackJob(ptr(weight), ptr(sigma), ptr(self.wp), ptr(self.wt), self.cout_real, self.cin_real, self.Co,
+                         self.Ci, self.k, self.k)
+
     def fwd(self, x, bias, out, stats):
         call("p2p_conv_fwd", C.byref(self.desc), ptr(x), ptr(self.wp), ptr(bias), ptr(out), ptr(stats),
              L.dtype_code(x.dtype), _state["impl"])
@@ -102,6 +110,13 @@ class ConvPlan:
         call("p2p_conv_wgrad", C.byref(self.desc), ptr(x), ptr(dout), ptr(acc), L.dtype_code(x.dtype), _state["impl"])
         call("p2p_unpack_wgrad", ptr(acc), ptr(grad), ptr(w_for_dot), ptr(sigma), ptr(dot), self.cout_real,
              self.cin_real, self.Co, self.Ci, self.k, self.k)
+
+    def wgrad_acc(self, x, dout, acc, grad, sigma=None, dot=None, w_for_dot=None) -> L.UnpackJob:
+        """Accumulate d loss / d weight into the zeroed fp32 scratch `acc` and return the job that moves it into
+        `grad` ([co][ci][kh][kw]); the caller runs all jobs of its pass in one p2p_unpack_wgrad_multi launch."""
+        call("p2p_conv_wgrad", C.byref(self.desc), ptr(x), ptr(dout), ptr(acc), L.dtype_code(x.dtype), _state["impl"])
+        return L.UnpackJob(ptr(acc), ptr(grad), ptr(w_for_dot), ptr(sigma), ptr(dot), self.cout_real, self.cin_real,
+                           self.Co, self.Ci, self.k, self.k)
 
 
 # =====================================================================================================
@@ -159,14 +174,25 @@ class GeneratorFunction(torch.autograd.Function):
         cin_real = 12
         block_in = block_in_src = long_skip = long_skip_src = None
         out = None
+        # all 24 filter banks are packed (both layouts) by one launch, and all BatchNorm sums live in one zeroed slab
+        packs, jobs, ci = [], [], 12
+        for (_n, _bn, cout, k, _s, _a, _r) in G_LAYERS:
+            pk = ConvPlan(1, k, k, pad16(ci), ci, cout, k, 1, 0)
+            jobs.append(pk.pack_job(params[4 * len(packs)], None, dt))
+            packs.append(pk)
+            ci = cout
+        L.call_multi("p2p_pack_weights_multi", jobs, dc)
+        stats_slab = _zeros((sum(2 * pk.Co for pk in packs),), torch.float64, dev) if training else None
+        stats_off = 0
         for li, (name, _bn, cout, k, stride, act, role) in enumerate(G_LAYERS):
             w, b, gamma, beta = params[4 * li: 4 * li + 4]
             rm, rv, nbt = buffers[li]
             plan = ConvPlan(B, cur.shape[1], cur.shape[2], cur.shape[3], cin_real, cout, k, stride, 0)
-            plan.pack(w, None, dt)
+            plan.wp, plan.wt = packs[li].wp, packs[li].wt
             Ho, Wo, Co = plan.Ho, plan.Wo, plan.Co
             r = _empty((B, Ho, Wo, Co), dt, dev)
-            stats = _zeros((2 * Co,), torch.float64, dev) if training else None
+            stats = stats_slab[stats_off: stats_off + 2 * Co] if training else None
+            stats_off += 2 * Co
             plan.fwd(cur, b, r, stats)
             sb = _empty((4 * Co,), torch.float32, dev)
             call("p2p_bn_finalize", ptr(stats), B * Ho * Wo, ptr(gamma), ptr(beta), ptr(rm), ptr(rv), ptr(nbt), ptr(sb),
@@ -248,6 +274,7 @@ class GeneratorFunction(torch.autograd.Function):
             red_off[id(st)] = off
             off += 2 * st.C
         ret: List[Optional[torch.Tensor]] = [None] * (4 * G_N)
+        unpack_jobs = []
         dpad = None            # gradient w.r.t. the (padded) buffer the stage being processed wrote
         extra = {}             # id(stage) -> compact gradients addressed to that stage's output (skip paths)
         for st in reversed(stages):
@@ -277,12 +304,14 @@ class GeneratorFunction(torch.autograd.Function):
             gbe, ret[4 * li + 3] = _grad_slot(pbeta)
             call("p2p_bn_bwd_apply", ptr(dz), ptr(st.r), ptr(st.sb), ptr(red), ptr(dr), ptr(gg), ptr(gbe), ptr(gb),
                  B * st.H * st.W, st.C, st.c_real, dc)
-            st.plan.wgrad(st.x_in, dr, gw, acc=acc_slab[acc_off[id(st)]: acc_off[id(st)] + st.plan.acc_numel()])
+            unpack_jobs.append(st.plan.wgrad_acc(
+                st.x_in, dr, acc_slab[acc_off[id(st)]: acc_off[id(st)] + st.plan.acc_numel()], gw))
             if li > 0:
                 dpad = _empty(tuple(st.x_in.shape), dt, dev)
                 st.plan.dgrad(dr, dpad)
             else:
                 dpad = None
+        L.call_multi("p2p_unpack_wgrad_multi", unpack_jobs)
         gp, ret_p = _grad_slot(refs[0])
         call("p2p_prelu_grad_finish", ptr(dprelu), ptr(gp))
         ctx.stages = None
@@ -357,6 +386,16 @@ class DiscriminatorFunction(torch.autograd.Function):
             call("p2p_avgpool3s2_fwd", ptr(xs32[-1]), ptr(nx), B, h, w, 8)
             xs32.append(nx)
         outs, plans, inputs = [], [], []
+        # every filter bank of the three scales (divided by its sigma) is packed by one launch
+        packs, jobs = {}, []
+        for sc in range(NUM_D):
+            ci = ca + cb
+            for j, (_cin, cout, _stride, _sn) in enumerate(layer_cfg):
+                pk = ConvPlan(1, 4, 4, pad16(ci), ci, cout, 4, 1, 2)
+                jobs.append(pk.pack_job(params[2 * (sc * nl + j)], sig_of.get((sc, j)), dt))
+                packs[(sc, j)] = pk
+                ci = cout
+        L.call_multi("p2p_pack_weights_multi", jobs, dc)
         for i in range(NUM_D):
             sc = NUM_D - 1 - i
             h, w = xs32[i].shape[1:3]
@@ -367,7 +406,7 @@ class DiscriminatorFunction(torch.autograd.Function):
                 wgt, bias = params[2 * (sc * nl + j)], params[2 * (sc * nl + j) + 1]
                 act = L.ACT_LRELU if j != nl - 1 else L.ACT_NONE
                 plan = ConvPlan(B, cur.shape[1], cur.shape[2], cur.shape[3], cin_real, cout, 4, stride, 2, act)
-                plan.pack(wgt, sig_of.get((sc, j)), dt)
+                plan.wp, plan.wt = packs[(sc, j)].wp, packs[(sc, j)].wt
                 o = _empty((B, plan.Ho, plan.Wo, plan.Co), dt, dev)
                 plan.fwd(cur, bias, o, None)
                 plans.append(plan)
@@ -402,7 +441,9 @@ class DiscriminatorFunction(torch.autograd.Function):
             for pl in plans:
                 acc_offs.append(off)
                 off += pl.acc_numel()
-            acc_slab = _zeros((off,), torch.float32, dev)
+            acc_slab = _zeros((off + len(sn_pos),), torch.float32, dev)   # + one dot product per spectral-norm layer
+            dots = acc_slab[off:]
+        unpack_jobs, sn_jobs = [], []
         dx32 = [None] * NUM_D       # fp32 gradient of each pyramid level (only when need_b)
         for i in reversed(range(NUM_D)):
             sc = NUM_D - 1 - i
@@ -428,17 +469,17 @@ class DiscriminatorFunction(torch.autograd.Function):
                 if need_w[k]:
                     pw = refs[2 * k]
                     gw, ret[2 * k] = _grad_slot(pw)
+                    acc = acc_slab[acc_offs[idx]: acc_offs[idx] + plan.acc_numel()]
                     if layer_cfg[j][3]:
                         sigma = ctx.sig_of[(sc, j)]
-                        dot = _zeros((1,), torch.float32, dev)
+                        dot = dots[sn_pos[(sc, j)]: sn_pos[(sc, j)] + 1]
                         # gW_bar = gW / sigma - (sum gW * W_bar) / sigma^2 * u v^T   (W = W_bar / sigma)
-                        plan.wgrad(x_in, dz, gw, sigma=sigma, dot=dot, w_for_dot=pw.detach(),
-                                   acc=acc_slab[acc_offs[idx]: acc_offs[idx] + plan.acc_numel()])
-                        u, v = ctx.sn_bufs[sn_pos[(sc, j)]]      # read NOW, not at forward: quirk Q1
-                        call("p2p_sn_weight_grad", ptr(gw), ptr(dot), ptr(sigma), ptr(u), ptr(v), pw.shape[0],
-                             pw[0].numel())
+                        unpack_jobs.append(plan.wgrad_acc(x_in, dz, acc, gw, sigma=sigma, dot=dot, w_for_dot=pw.detach()))
+                        u, v = ctx.sn_bufs[sn_pos[(sc, j)]]      # read at backward time: quirk Q1
+                        sn_jobs.append(L.SnGradJob(ptr(gw), ptr(dot), ptr(sigma), ptr(u), ptr(v), pw.shape[0],
+                                                   pw[0].numel()))
                     else:
-                        plan.wgrad(x_in, dz, gw, acc=acc_slab[acc_offs[idx]: acc_offs[idx] + plan.acc_numel()])
+                        unpack_jobs.append(plan.wgrad_acc(x_in, dz, acc, gw))
                 if j > 0 or need_b:
                     g_next = _empty(tuple(x_in.shape), dt, dev)
                     plan.dgrad(dz, g_next)
@@ -449,6 +490,10 @@ class DiscriminatorFunction(torch.autograd.Function):
                 d32 = _zeros((B, h, w, 8), torch.float32, dev)
                 call("p2p_uncast_add", ptr(g_next), ptr(d32), B * h * w, 8, 16, dc)
                 dx32[i] = d32
+        if unpack_jobs:
+            L.call_multi("p2p_unpack_wgrad_multi", unpack_jobs)
+        if sn_jobs:
+            L.call_multi("p2p_sn_weight_grad_multi", sn_jobs)
         ga = gb = None
         if need_b:
             # fold the pyramid: d level i += avgpool_backward(d level i+1)

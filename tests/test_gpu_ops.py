@@ -307,3 +307,55 @@ def test_spectral_norm_power_iteration():
         s_ref = u_ref.dot(w2.mv(v_ref))
         assert relerr(v, v_ref) <= 1e-5 and relerr(u, u_ref) <= 1e-5
         assert abs(s.item() - s_ref.item()) <= 1e-5 * abs(s_ref.item())
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+def test_batched_pack_unpack_and_sigma_correction_match_single_calls(dt):
+    """p2p_pack_weights_multi / p2p_unpack_wgrad_multi / p2p_sn_weight_grad_multi == the per-layer entry points."""
+    from p2p_pytorch_b200._lib import call, call_multi, ptr
+    torch.manual_seed(9)
+    shapes = [(32, 12, 9), (128, 128, 3), (3, 32, 9), (64, 6, 4), (512, 256, 4), (1, 512, 4)]   # (cout, cin, k)
+    dc = L.dtype_code(dt)
+    pack_jobs, singles, keep = [], [], []
+    for cout, cin, k in shapes:
+        w = torch.randn(cout, cin, k, k, device=DEV) * 0.1
+        sigma = torch.rand(1, device=DEV) + 0.5 if cout % 2 == 0 else None
+        Co, Ci = E.pad16(cout), E.pad16(cin)
+        a = [torch.full((Co, k, k, Ci), 7.0, dtype=dt, device=DEV), torch.full((Ci, k, k, Co), 7.0, dtype=dt, device=DEV)]
+        b = [torch.full_like(a[0], 9.0), torch.full_like(a[1], 9.0)]
+        want_wt = cout != 3
+        pack_jobs.append(L.PackJob(ptr(w), ptr(sigma), ptr(a[0]), ptr(a[1]) if want_wt else None, cout, cin, Co, Ci, k, k))
+        call("p2p_pack_weights", ptr(w), ptr(sigma), ptr(b[0]), ptr(b[1]) if want_wt else None, cout, cin, Co, Ci, k, k, dc)
+        singles.append((a, b, want_wt))
+        keep.append((w, sigma))
+    call_multi("p2p_pack_weights_multi", pack_jobs, dc)
+    for a, b, want_wt in singles:
+        assert torch.equal(a[0], b[0])
+        assert torch.equal(a[1], b[1]) if want_wt else bool((a[1] == 7.0).all())
+
+    unpack_jobs, sn_jobs, checks = [], [], []
+    for (cout, cin, k), (w, sigma) in zip(shapes, keep):
+        Co, Ci = E.pad16(cout), E.pad16(cin)
+        acc = torch.randn(k, k, Ci, Co, device=DEV)
+        g0 = torch.randn(cout, cin, k, k, device=DEV)
+        g_multi, g_single = g0.clone(), g0.clone()
+        dot_m = torch.zeros(1, device=DEV) if sigma is not None else None
+        dot_s = torch.zeros(1, device=DEV) if sigma is not None else None
+        unpack_jobs.append(L.UnpackJob(ptr(acc), ptr(g_multi), ptr(w), ptr(sigma), ptr(dot_m), cout, cin, Co, Ci, k, k))
+        call("p2p_unpack_wgrad", ptr(acc), ptr(g_single), ptr(w), ptr(sigma), ptr(dot_s), cout, cin, Co, Ci, k, k)
+        u = v = None
+        if sigma is not None:
+            u, v = torch.randn(cout, device=DEV), torch.randn(cin * k * k, device=DEV)
+            sn_jobs.append(L.SnGradJob(ptr(g_multi), ptr(dot_m), ptr(sigma), ptr(u), ptr(v), cout, cin * k * k))
+        checks.append((acc, g_multi, g_single, dot_m, dot_s, sigma, u, v, cout, cin, k))
+    call_multi("p2p_unpack_wgrad_multi", unpack_jobs)
+    for acc, g_multi, g_single, dot_m, dot_s, sigma, u, v, cout, cin, k in checks:
+        if sigma is None:
+            assert torch.equal(g_multi, g_single)
+        else:
+            assert relerr(g_multi, g_single) <= 1e-6
+            assert abs(dot_m.item() - dot_s.item()) <= 1e-4 * max(abs(dot_s.item()), 1.0)
+            call("p2p_sn_weight_grad", ptr(g_single), ptr(dot_s), ptr(sigma), ptr(u), ptr(v), cout, cin * k * k)
+    call_multi("p2p_sn_weight_grad_multi", sn_jobs)
+    for acc, g_multi, g_single, dot_m, dot_s, sigma, u, v, cout, cin, k in checks:
+        assert relerr(g_multi, g_single) <= 1e-4
