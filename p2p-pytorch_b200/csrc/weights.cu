@@ -74,48 +74,113 @@ struct PackTable { p2p_pack_job j[P2P_MULTI_MAX]; };
 struct UnpackTable { p2p_unpack_job j[P2P_MULTI_MAX]; };
 struct SnGradTable { p2p_sn_grad_job j[P2P_MULTI_MAX]; };
 
+// Both directions are a [columns x taps] <-> [taps x columns] transpose per (row, column chunk), staged in shared
+// memory so that global reads AND writes are coalesced runs (a thread-per-element gather is L1-tag bound: measured
+// 76 us for the discriminator's 68 MB instead of ~15).  Rows of the tile are padded to taps + 1 floats.
+constexpr int kTileFloats = 8192;
+
+__device__ __forceinline__ int tile_cols(int Cc, int taps) {
+  int cw = kTileFloats / (taps + 1);
+  cw = cw > 256 ? 256 : cw & ~15;
+  return Cc < cw ? Cc : cw;
+}
+
+// Element e of a [ncol x taps] tile in (column, tap) order and in (tap, column) order, advanced by 256 per step
+// without divisions in the loops (a division per element made the first version instruction-bound: IPC 3.1).
+struct Walk {
+  int a, b, da, db, nb;        // e = a * nb + b;  e += 256  ->  a += da, b += db with carry
+  __device__ __forceinline__ Walk(int e0, int nb_) : nb(nb_) { a = e0 / nb_; b = e0 - a * nb_; da = 256 / nb_; db = 256 - da * nb_; }
+  __device__ __forceinline__ void step() { a += da; b += db; if (b >= nb) { b -= nb; ++a; } }
+};
+
+// dst[(r * taps + t) * Cc + c] = inv * w[co][ci][t]  for the columns c of one chunk;  (co, ci) = (r, c) or (c, r)
 template <typename T>
-__global__ void __launch_bounds__(256) pack_weights_multi_kernel(const __grid_constant__ PackTable tb) {
-  const p2p_pack_job& jb = tb.j[blockIdx.y];
-  const float* __restrict__ w = jb.w;
-  T* __restrict__ wp = static_cast<T*>(jb.w_packed);
-  T* __restrict__ wt = static_cast<T*>(jb.wt_packed);
-  const float inv = jb.sigma != nullptr ? 1.f / *jb.sigma : 1.f;
-  const uint32_t Ci = jb.Ci, Co = jb.Co, taps = jb.kh * jb.kw, ci_real = jb.ci_real, co_real = jb.co_real;
-  const uint32_t total = Co * taps * Ci;                       // < 2^31, checked by the caller
-  for (uint32_t i = blockIdx.x * 256 + threadIdx.x; i < total; i += gridDim.x * 256) {
-    if (wp != nullptr) {  // i enumerates [Co][tap][Ci]
-      const uint32_t ci = i % Ci, q = i / Ci;
-      const uint32_t tap = q % taps, co = q / taps;
-      const float v = (co < co_real && ci < ci_real) ? w[(co * ci_real + ci) * taps + tap] * inv : 0.f;
-      stf(wp + i, v);
+__device__ __forceinline__ void pack_layout(float* tile, const float* __restrict__ w, float inv, T* __restrict__ dst,
+                                            int R, int Cc, int r_real, int c_real, int taps, int ci_real,
+                                            bool rows_are_co) {
+  const int cw = tile_cols(Cc, taps), pitch = taps + 1;
+  const int chunks = (Cc + cw - 1) / cw, items = R * chunks;
+  const uint32_t cstride = rows_are_co ? (uint32_t)taps : (uint32_t)ci_real * taps;   // floats between columns
+  const Walk ld0(threadIdx.x, taps);           // (column, tap)
+  const Walk st_full(threadIdx.x, cw);         // (tap, column) for full chunks
+  for (int item = blockIdx.x; item < items; item += gridDim.x) {
+    const int r = item / chunks, c0 = (item - r * chunks) * cw;
+    const int ncol = min(cw, Cc - c0), n = ncol * taps;
+    const float* src = rows_are_co ? w + ((uint32_t)r * ci_real + c0) * (uint32_t)taps
+                                   : w + ((uint32_t)c0 * ci_real + r) * (uint32_t)taps;
+    const bool row_ok = r < r_real;
+    __syncthreads();
+    Walk ld = ld0;
+#pragma unroll 4
+    for (int e = threadIdx.x; e < n; e += 256) {
+      tile[ld.a * pitch + ld.b] = (row_ok && c0 + ld.a < c_real) ? src[ld.a * cstride + ld.b] * inv : 0.f;
+      ld.step();
     }
-    if (wt != nullptr) {  // i enumerates [Ci][tap][Co]
-      const uint32_t co = i % Co, q = i / Co;
-      const uint32_t tap = q % taps, ci = q / taps;
-      const float v = (co < co_real && ci < ci_real) ? w[(co * ci_real + ci) * taps + tap] * inv : 0.f;
-      stf(wt + i, v);
+    __syncthreads();
+    T* d = dst + (uint32_t)r * taps * Cc + c0;
+    Walk st = ncol == cw ? st_full : Walk(threadIdx.x, ncol);
+#pragma unroll 4
+    for (int e = threadIdx.x; e < n; e += 256) {
+      stf(d + (uint32_t)st.a * Cc + st.b, tile[st.b * pitch + st.a]);
+      st.step();
     }
   }
 }
 
+template <typename T>
+__global__ void __launch_bounds__(256) pack_weights_multi_kernel(const __grid_constant__ PackTable tb) {
+  __shared__ float tile[kTileFloats];
+  const p2p_pack_job& jb = tb.j[blockIdx.y];
+  const float inv = jb.sigma != nullptr ? 1.f / *jb.sigma : 1.f;
+  const int taps = jb.kh * jb.kw;
+  if (jb.w_packed != nullptr)   // [Co][tap][Ci]
+    pack_layout<T>(tile, jb.w, inv, static_cast<T*>(jb.w_packed), jb.Co, jb.Ci, jb.co_real, jb.ci_real, taps, jb.ci_real,
+                   true);
+  if (jb.wt_packed != nullptr)  // [Ci][tap][Co]
+    pack_layout<T>(tile, jb.w, inv, static_cast<T*>(jb.wt_packed), jb.Ci, jb.Co, jb.ci_real, jb.co_real, taps, jb.ci_real,
+                   false);
+}
+
+// grad[co][ci][:] += scale * acc[:][ci][co]: per (ci, chunk of co) the tile is read along co and written as runs of taps
 __global__ void __launch_bounds__(256) unpack_wgrad_multi_kernel(const __grid_constant__ UnpackTable tb) {
+  __shared__ float tile[kTileFloats];
   const p2p_unpack_job& jb = tb.j[blockIdx.y];
   const float* __restrict__ acc = jb.dw_acc;
-  const float* __restrict__ w = jb.w;
   float* __restrict__ grad = jb.grad;
+  const float* __restrict__ w = jb.w;
+  const bool want_dot = jb.dot != nullptr;
   const float scale = jb.sigma != nullptr ? 1.f / *jb.sigma : 1.f;
-  const uint32_t Ci = jb.Ci, Co = jb.Co, taps = jb.kh * jb.kw, ci_real = jb.ci_real;
-  const uint32_t total = (uint32_t)jb.co_real * ci_real * taps;
+  const int Ci = jb.Ci, Co = jb.Co, taps = jb.kh * jb.kw, ci_real = jb.ci_real, co_real = jb.co_real;
+  const int cw = tile_cols(co_real, taps), pitch = taps + 1;
+  const int chunks = (co_real + cw - 1) / cw, items = ci_real * chunks;
+  const uint32_t tap_stride = (uint32_t)Ci * Co, col_stride = (uint32_t)ci_real * taps;
+  const Walk st0(threadIdx.x, taps);           // (column, tap)
+  const Walk ld_full(threadIdx.x, cw);         // (tap, column) for full chunks
   float d = 0.f;
-  for (uint32_t i = blockIdx.x * 256 + threadIdx.x; i < total; i += gridDim.x * 256) {
-    const uint32_t tap = i % taps, q = i / taps;
-    const uint32_t ci = q % ci_real, co = q / ci_real;
-    const float a = acc[(tap * Ci + ci) * Co + co];
-    grad[i] += a * scale;
-    if (jb.dot != nullptr) d += a * w[i];
+  for (int item = blockIdx.x; item < items; item += gridDim.x) {
+    const int ci = item / chunks, c0 = (item - ci * chunks) * cw;
+    const int ncol = min(cw, co_real - c0), n = ncol * taps;
+    const float* a = acc + (uint32_t)ci * Co + c0;
+    __syncthreads();
+    Walk ld = ncol == cw ? ld_full : Walk(threadIdx.x, ncol);
+#pragma unroll 4
+    for (int e = threadIdx.x; e < n; e += 256) {
+      tile[ld.b * pitch + ld.a] = a[ld.a * tap_stride + ld.b];
+      ld.step();
+    }
+    __syncthreads();
+    const uint32_t g0 = ((uint32_t)c0 * ci_real + ci) * (uint32_t)taps;
+    Walk st = st0;
+#pragma unroll 4
+    for (int e = threadIdx.x; e < n; e += 256) {
+      const uint32_t g = g0 + st.a * col_stride + st.b;
+      const float v = tile[st.a * pitch + st.b];
+      grad[g] += v * scale;
+      if (want_dot) d += v * w[g];
+      st.step();
+    }
   }
-  if (jb.dot != nullptr) {                                    // uniform per block row
+  if (want_dot) {                                             // uniform per block row
     const float tot = block_sum<float>(d);
     if (threadIdx.x == 0 && tot != 0.f) atomicAdd(jb.dot, tot);
   }
@@ -133,8 +198,8 @@ __global__ void __launch_bounds__(256) sn_weight_grad_multi_kernel(const __grid_
 }
 
 static inline int multi_grid_x(int64_t max_total) {
-  int64_t x = (max_total + 256 * 8 - 1) / (256 * 8);
-  return (int)(x < 1 ? 1 : (x > 96 ? 96 : x));
+  int64_t x = (max_total + 4095) / 4096;                    // one item is a [<=256 columns x taps] tile
+  return (int)(x < 1 ? 1 : (x > 592 ? 592 : x));
 }
 
 // ---- batched power iteration ---------------------------------------------------------------------
