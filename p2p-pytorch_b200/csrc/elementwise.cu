@@ -2,11 +2,12 @@
 // train-mode BatchNorm (statistics finalisation, apply, backward), activations and their gradients,
 // the discriminator's input pyramid.  All kernels move 8 channels (16-32 bytes) per thread, channel-fastest,
 // so every warp access is a run of full 32-byte sectors.
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace p2p {
 
-__device__ int g_dbg_no_atomics = 0;   // timing experiment switch (P2P_DEBUG_NO_RED_ATOMICS=1)
 
 // =================================================================================================
 // generator input: PixelUnshuffle(2) -> nearest x2 -> ReflectionPad(4)   (networks.py:173-187,457,399)
@@ -208,144 +209,204 @@ __device__ __forceinline__ void fold_extra(int u, int n, int pad, int out[2]) {
   out[1] = (u <= n - 2 && u >= n - 1 - pad) ? 2 * (n - 1) - u + pad : -1;         // bottom / right halo
 }
 
-// backward pass 1 (see header).  One thread per source pixel x 8 channels; block = 256 threads laid out
-// as (C/8 channel groups) x (256/(C/8) pixel lanes) so the per-channel partial sums reduce through smem.
-// All loads of an item (up to 8 x 16 bytes) are issued before the first use; the reflection halo, which only
-// border pixels have, is a separate rarely-taken path.
-template <typename T, int ACT>
-__global__ void __launch_bounds__(256, 3)
+// raw 4-channel vector
+template <typename T> struct Raw4;
+template <> struct Raw4<float> {
+  float4 a;
+  __device__ __forceinline__ void load(const float* p) { a = *reinterpret_cast<const float4*>(p); }
+  __device__ __forceinline__ void get(float v[4]) const { v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; }
+  static __device__ __forceinline__ void store(float* p, const float v[4]) {
+    *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+  }
+};
+template <> struct Raw4<__nv_bfloat16> {
+  uint2 u;
+  __device__ __forceinline__ void load(const __nv_bfloat16* p) { u = *reinterpret_cast<const uint2*>(p); }
+  __device__ __forceinline__ void get(float v[4]) const {
+    v[0] = __uint_as_float(u.x << 16); v[1] = __uint_as_float(u.x & 0xffff0000u);
+    v[2] = __uint_as_float(u.y << 16); v[3] = __uint_as_float(u.y & 0xffff0000u);
+  }
+  static __device__ __forceinline__ void store(__nv_bfloat16* p, const float v[4]) {
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]), hi = __floats2bfloat162_rn(v[2], v[3]);
+    *reinterpret_cast<uint2*>(p) = make_uint2(*reinterpret_cast<uint32_t*>(&lo), *reinterpret_cast<uint32_t*>(&hi));
+  }
+};
+
+// Mirrored copies of source pixel (n, y, x) in the reflection halo of the padded gradient buffer, 4 channels.
+template <typename T>
+__device__ __forceinline__ void fold_halo_sum4(const T* __restrict__ dpad, int n, int y, int x, int up, int pad, int Hu,
+                                            int Wu, int Hd, int Wd, int C, int c0, float e[4]) {
+  e[0] = e[1] = e[2] = e[3] = 0.f;
+  for (int uy = y * up; uy < y * up + up; ++uy) {
+    int er[2];
+    fold_extra(uy, Hu, pad, er);
+    for (int ux = x * up; ux < x * up + up; ++ux) {
+      int ec[2];
+      fold_extra(ux, Wu, pad, ec);
+      // (extra row, own col), (own row, extra col), (extra row, extra col)
+      for (int ai = -1; ai < 2; ++ai) {
+        const int row = ai < 0 ? uy + pad : er[ai];
+        if (row < 0) continue;
+        for (int bi = -1; bi < 2; ++bi) {
+          if (ai < 0 && bi < 0) continue;          // the interior copy was already added
+          const int col = bi < 0 ? ux + pad : ec[bi];
+          if (col < 0) continue;
+          Raw4<T> h;
+          float t[4];
+          h.load(dpad + (((int64_t)n * Hd + row) * Wd + col) * C + c0);
+          h.get(t);
+          e[0] += t[0]; e[1] += t[1]; e[2] += t[2]; e[3] += t[3];
+        }
+      }
+    }
+  }
+}
+
+// backward pass 1 (see header).  One thread per source pixel x FOUR channels (8-byte loads; a warp still covers
+// whole 32-byte sectors): the per-thread state is small enough for 4 resident blocks per SM without spilling --
+// the 8-channel version needed 80+ registers, spilled inside the loop (3 M local-store sectors per launch) and ran
+// at 2 TB/s.  Optional inputs sit behind warp-uniform branches, (n, y, x) advance without divisions, the per-
+// channel scale/shift come from shared memory, and the second sum runs on the raw conv output:
+// sum dz*xhat = istd * (sum dz*r - mean * sum dz) is formed once per block in double.
+template <typename T, int ACT, int UP>
+__global__ void __launch_bounds__(256, 4)
     bn_act_bwd_reduce_kernel(const T* __restrict__ dpad, const T* __restrict__ g1, const T* __restrict__ g2,
                              const float* __restrict__ g_nchw, const T* __restrict__ r, const float* __restrict__ sb,
                              const T* __restrict__ skip, int skip_pad, const float* __restrict__ prelu_a,
                              T* __restrict__ dz, double* __restrict__ red, double* __restrict__ dprelu, int B, int H,
-                             int W, int C, int c_real, int up, int pad) {
+                             int W, int C, int c_real, int pad) {
   constexpr int act = ACT;
-  const int C8 = C >> 3;
-  const int c8 = threadIdx.x % C8, lane_p = threadIdx.x / C8, ppb = 256 / C8;
-  const int Hu = H * up, Wu = W * up, Hd = Hu + 2 * pad, Wd = Wu + 2 * pad;
+  const int C4 = C >> 2;
+  const int c4 = threadIdx.x % C4, lane_p = threadIdx.x / C4, ppb = 256 / C4;
+  const int c0 = c4 * 4;
+  const int Hu = H * UP, Wu = W * UP, Hd = Hu + 2 * pad, Wd = Wu + 2 * pad;
+  const int Hs = H + 2 * skip_pad, Ws = W + 2 * skip_pad;
   const float a = prelu_a != nullptr ? *prelu_a : 0.f;
   const uint32_t pixels = (uint32_t)B * H * W;   // < 2^31, checked by the caller
-  float s1[8], s2[8];
-  float sa = 0.f;
-#pragma unroll
-  for (int k = 0; k < 8; ++k) s1[k] = s2[k] = 0.f;
-  // per-channel constants of this thread
-  float sc[8], sh_[8], mean[8], istd[8];
-#pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    const int c = c8 * 8 + k;
-    sc[k] = sb != nullptr ? sb[c] : 1.f;
-    sh_[k] = sb != nullptr ? sb[C + c] : 0.f;
-    mean[k] = sb != nullptr ? sb[2 * C + c] : 0.f;
-    istd[k] = sb != nullptr ? sb[3 * C + c] : 0.f;
+  __shared__ __align__(16) float s_sc[512], s_sh[512];
+  for (int c = threadIdx.x; c < C; c += 256) {
+    s_sc[c] = sb != nullptr ? sb[c] : 1.f;
+    s_sh[c] = sb != nullptr ? sb[C + c] : 0.f;
   }
-  for (uint32_t p = blockIdx.x * ppb + lane_p; p < pixels; p += gridDim.x * ppb) {
-    const int x = (int)(p % (uint32_t)W);
-    const uint32_t pq = p / (uint32_t)W;
-    const int y = (int)(pq % (uint32_t)H);
-    const int n = (int)(pq / (uint32_t)H);
-    // ---- issue every load first ----
-    Raw8<T> d00, d01, d10, d11, q1, q2, rr, sk;
-    d00.zero(); d01.zero(); d10.zero(); d11.zero(); q1.zero(); q2.zero(); sk.zero();
-    const T* dbase = nullptr;
-    if (dpad != nullptr) {
-      dbase = dpad + (((int64_t)n * Hd + y * up + pad) * Wd + x * up + pad) * C + c8 * 8;
-      d00.load(dbase);
-      if (up == 2) {
-        d01.load(dbase + C);
-        d10.load(dbase + (int64_t)Wd * C);
-        d11.load(dbase + (int64_t)Wd * C + C);
-      }
-    }
-    if (g1 != nullptr) q1.load(g1 + (size_t)p * C + c8 * 8);
-    if (g2 != nullptr) q2.load(g2 + (size_t)p * C + c8 * 8);
-    rr.load(r + (size_t)p * C + c8 * 8);
-    if (skip != nullptr)
-      sk.load(skip + (((int64_t)n * (H + 2 * skip_pad) + y + skip_pad) * (W + 2 * skip_pad) + x + skip_pad) * C + c8 * 8);
-    // ---- combine ----
-    float g[8], t[8];
-    d00.get(g);
-    if (up == 2) {
-      d01.get(t);
-#pragma unroll
-      for (int k = 0; k < 8; ++k) g[k] += t[k];
-      d10.get(t);
-#pragma unroll
-      for (int k = 0; k < 8; ++k) g[k] += t[k];
-      d11.get(t);
-#pragma unroll
-      for (int k = 0; k < 8; ++k) g[k] += t[k];
-    }
-    q1.get(t);
-#pragma unroll
-    for (int k = 0; k < 8; ++k) g[k] += t[k];
-    q2.get(t);
-#pragma unroll
-    for (int k = 0; k < 8; ++k) g[k] += t[k];
-    // reflection halo: only pixels within `pad` of the border have mirrored copies
-    if (dpad != nullptr && pad > 0) {
-      const int uy0 = y * up, ux0 = x * up;
-      const bool near = uy0 <= pad || uy0 + up - 1 >= Hu - 1 - pad || ux0 <= pad || ux0 + up - 1 >= Wu - 1 - pad;
-      if (near) {
-        for (int uy = uy0; uy < uy0 + up; ++uy) {
-          int er[2];
-          fold_extra(uy, Hu, pad, er);
-          for (int ux = ux0; ux < ux0 + up; ++ux) {
-            int ec[2];
-            fold_extra(ux, Wu, pad, ec);
-            // (extra row, own col), (own row, extra col), (extra row, extra col)
-#pragma unroll
-            for (int ai = -1; ai < 2; ++ai) {
-              const int row = ai < 0 ? uy + pad : er[ai];
-              if (row < 0) continue;
-#pragma unroll
-              for (int bi = -1; bi < 2; ++bi) {
-                if (ai < 0 && bi < 0) continue;          // the interior copy was already added
-                const int col = bi < 0 ? ux + pad : ec[bi];
-                if (col < 0) continue;
-                ld8(dpad + (((int64_t)n * Hd + row) * Wd + col) * C + c8 * 8, t);
-#pragma unroll
-                for (int k = 0; k < 8; ++k) g[k] += t[k];
-              }
-            }
-          }
+  __syncthreads();
+  float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
+  float sa = 0.f;
+  const int n_ok = c_real - c0;                  // channels k < n_ok of this thread are real
+  uint32_t p = blockIdx.x * ppb + lane_p;
+  const uint32_t step = gridDim.x * ppb;
+  int x = (int)(p % (uint32_t)W), y = (int)((p / (uint32_t)W) % (uint32_t)H), n = (int)(p / ((uint32_t)W * H));
+  const int dx = (int)(step % (uint32_t)W), dy = (int)((step / (uint32_t)W) % (uint32_t)H),
+            dn = (int)(step / ((uint32_t)W * H));
+  // Pixels within `pad` of the border also collect the mirrored copies of the reflection halo.  They are a few
+  // percent of the map and take a second loop of their own, so that the halo code (and its register pressure)
+  // stays out of the streaming loop.
+  const bool has_halo = dpad != nullptr && pad > 0;
+  auto near_border = [&](int y_, int x_) {
+    const int uy0 = y_ * UP, ux0 = x_ * UP;
+    return uy0 <= pad || uy0 + UP - 1 >= Hu - 1 - pad || ux0 <= pad || ux0 + UP - 1 >= Wu - 1 - pad;
+  };
+  auto item = [&](auto fold_tag, uint32_t p, int n, int y, int x) {
+      // ---- issue every load first ----
+      Raw4<T> d00, d01, d10, d11, q1, q2, rr, sk;
+      const size_t off = (size_t)p * C + c0;
+      rr.load(r + off);
+      if (dpad != nullptr) {
+        const T* dbase = dpad + (((size_t)n * Hd + y * UP + pad) * Wd + x * UP + pad) * C + c0;
+        d00.load(dbase);
+        if (UP == 2) {
+          d01.load(dbase + C);
+          d10.load(dbase + (size_t)Wd * C);
+          d11.load(dbase + (size_t)Wd * C + C);
         }
       }
-    }
-    if (g_nchw != nullptr) {
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        const int c = c8 * 8 + k;
-        if (c < c_real) g[k] += g_nchw[(((int64_t)n * c_real + c) * H + y) * W + x];
+      if (g1 != nullptr) q1.load(g1 + off);
+      if (g2 != nullptr) q2.load(g2 + off);
+      if (skip != nullptr) sk.load(skip + (((size_t)n * Hs + y + skip_pad) * Ws + x + skip_pad) * C + c0);
+      // ---- combine the incoming gradients ----
+      float g[4] = {0.f, 0.f, 0.f, 0.f}, t[4];
+      if (dpad != nullptr) {
+        d00.get(g);
+        if (UP == 2) {
+          d01.get(t); g[0] += t[0]; g[1] += t[1]; g[2] += t[2]; g[3] += t[3];
+          d10.get(t); g[0] += t[0]; g[1] += t[1]; g[2] += t[2]; g[3] += t[3];
+          d11.get(t); g[0] += t[0]; g[1] += t[1]; g[2] += t[2]; g[3] += t[3];
+        }
+        if (decltype(fold_tag)::value) {
+          float e[4];
+          fold_halo_sum4<T>(dpad, n, y, x, UP, pad, Hu, Wu, Hd, Wd, C, c0, e);
+          g[0] += e[0]; g[1] += e[1]; g[2] += e[2]; g[3] += e[3];
+        }
       }
+      if (g1 != nullptr) { q1.get(t); g[0] += t[0]; g[1] += t[1]; g[2] += t[2]; g[3] += t[3]; }
+      if (g2 != nullptr) { q2.get(t); g[0] += t[0]; g[1] += t[1]; g[2] += t[2]; g[3] += t[3]; }
+      if (g_nchw != nullptr) {
+  #pragma unroll
+        for (int k = 0; k < 4; ++k)
+          if (k < n_ok) g[k] += g_nchw[(((size_t)n * c_real + c0 + k) * H + y) * W + x];
+      }
+      // ---- through the activation, sums ----
+      float rv[4], o[4];
+      rr.get(rv);
+      if (act != P2P_ACT_NONE) {
+        float skv[4] = {0.f, 0.f, 0.f, 0.f};
+        if (skip != nullptr) sk.get(skv);
+        const float4 sc = *reinterpret_cast<const float4*>(s_sc + c0), sf = *reinterpret_cast<const float4*>(s_sh + c0);
+        const float scv[4] = {sc.x, sc.y, sc.z, sc.w}, sfv[4] = {sf.x, sf.y, sf.z, sf.w};
+  #pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float z = fmaf(rv[k], scv[k], sfv[k]) + skv[k];
+          if (act == P2P_ACT_PRELU && z < 0.f && k < n_ok) sa += g[k] * z;
+          g[k] *= act_bwd(z, act, a);
+        }
+      }
+  #pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float d = k < n_ok ? g[k] : 0.f;
+        o[k] = d;
+        const float dq = round_as(d, dz);
+        s1[k] += dq;
+        s2[k] = fmaf(dq, rv[k], s2[k]);
+      }
+      Raw4<T>::store(dz + off, o);
+  };
+  auto advance = [&](int& n_, int& y_, int& x_) {
+    x_ += dx;
+    if (x_ >= W) { x_ -= W; ++y_; }
+    y_ += dy;
+    if (y_ >= H) { y_ -= H; ++n_; }
+    n_ += dn;
+  };
+  const uint32_t p0 = p;
+  const int x0 = x, y0 = y, n0 = n;
+  for (; p < pixels; p += step) {
+    if (!(has_halo && near_border(y, x))) item(std::false_type{}, p, n, y, x);
+    advance(n, y, x);
+  }
+  if (has_halo) {
+    p = p0; x = x0; y = y0; n = n0;
+    for (; p < pixels; p += step) {
+      if (near_border(y, x)) item(std::true_type{}, p, n, y, x);
+      advance(n, y, x);
     }
-    float rv[8], skv[8], o[8];
-    rr.get(rv);
-    sk.get(skv);
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const int c = c8 * 8 + k;
-      const float z = fmaf(rv[k], sc[k], sh_[k]) + skv[k];
-      const float d = (c < c_real) ? g[k] * act_bwd(z, act, a) : 0.f;
-      if (act == P2P_ACT_PRELU && z < 0.f && c < c_real) sa += g[k] * z;
-      o[k] = d;
-      const float dq = round_as(d, dz);
-      s1[k] += dq;
-      s2[k] += dq * (rv[k] - mean[k]) * istd[k];
-    }
-    st8(dz + (size_t)p * C + c8 * 8, o);
   }
   if (red != nullptr) {
-    __shared__ float sh[2][8][256];
+    __shared__ float sh[2][256 * 5];           // [which][thread * 5 + k]: conflict-free writes and column reads
 #pragma unroll
-    for (int k = 0; k < 8; ++k) { sh[0][k][threadIdx.x] = s1[k]; sh[1][k][threadIdx.x] = s2[k]; }
+    for (int k = 0; k < 4; ++k) { sh[0][threadIdx.x * 5 + k] = s1[k]; sh[1][threadIdx.x * 5 + k] = s2[k]; }
     __syncthreads();
-    for (int t = threadIdx.x; t < 2 * C; t += 256) {
-      const int which = t / C, c = t % C;
-      double acc = 0.0;
-      for (int l = 0; l < ppb; ++l) acc += (double)sh[which][c & 7][l * C8 + (c >> 3)];
-      if (!g_dbg_no_atomics) atomicAdd(red + which * C + c, acc);
-      else if (acc == 1.2345) red[0] = acc;
+    for (int c = threadIdx.x; c < C; c += 256) {
+      double a1 = 0.0, a2 = 0.0;
+      for (int l = 0; l < ppb; ++l) {
+        const int idx = (l * C4 + (c >> 2)) * 5 + (c & 3);
+        a1 += (double)sh[0][idx];
+        a2 += (double)sh[1][idx];
+      }
+      if (c < c_real) {
+        const double mean = sb != nullptr ? (double)sb[2 * C + c] : 0.0;
+        const double istd = sb != nullptr ? (double)sb[3 * C + c] : 0.0;
+        atomicAdd(red + c, a1);
+        atomicAdd(red + C + c, istd * (a2 - mean * a1));
+      }
     }
   }
   if (dprelu != nullptr && act == P2P_ACT_PRELU) {
@@ -697,16 +758,6 @@ int p2p_bn_act_store(const void* r, const float* sb, const void* skip, int skip_
   P2P_LAUNCH_CHECK();
 }
 
-static void dbg_init() {
-  static bool done = false;
-  if (!done) {
-    const char* e = getenv("P2P_DEBUG_NO_RED_ATOMICS");
-    const int v = (e != nullptr && e[0] == '1') ? 1 : 0;
-    cudaMemcpyToSymbol(p2p::g_dbg_no_atomics, &v, sizeof(int));
-    done = true;
-  }
-}
-
 int p2p_bn_act_bwd_reduce(const void* dpad, const void* g1, const void* g2, const float* g_nchw, const void* r,
                           const float* sb, const void* skip, int skip_pad, const float* prelu_a, void* dz, double* red,
                           double* dprelu, int B, int H, int W, int C, int c_real, int act, int up, int pad, int dtype,
@@ -715,14 +766,19 @@ int p2p_bn_act_bwd_reduce(const void* dpad, const void* g1, const void* g2, cons
   P2P_REQUIRE(dpad || g1 || g2 || g_nchw, "no incoming gradient");
   P2P_REQUIRE(C % 16 == 0 && C <= 512 && (up == 1 || up == 2), "bad geometry");
   P2P_REQUIRE(act != P2P_ACT_PRELU || prelu_a, "PReLU needs its slope");
-  const int ppb = 256 / (C / 8);
+  P2P_REQUIRE(256 % (C / 4) == 0, "C must be 16, 32, 64, 128, 256 or 512");
+  const int ppb = 256 / (C / 4);
   const int64_t pixels = (int64_t)B * H * W;
-  dbg_init();
-  P2P_REQUIRE((int64_t)B * (H * up + 2 * pad) * (W * up + 2 * pad) * (C / 8) < (1LL << 31), "tensor too large");
-#define P2P_BWD_REDUCE(ACT_)                                                                                     \
-  P2P_DISPATCH(dtype, bn_act_bwd_reduce_kernel<T, ACT_><<<red_ew_grid(pixels, ppb), 256, 0, as_stream(stream)>>>( \
+  static const int bps = getenv("P2P_RED_BPS") ? atoi(getenv("P2P_RED_BPS")) : 4;
+  const int64_t want = (pixels + ppb - 1) / ppb;
+  const int grid = (int)(want < (int64_t)kSMs * bps ? want : (int64_t)kSMs * bps);
+#define P2P_BWD_REDUCE_U(ACT_, UP_)                                                                              \
+  P2P_DISPATCH(dtype, bn_act_bwd_reduce_kernel<T, ACT_, UP_><<<grid, 256, 0, as_stream(stream)>>>(               \
                           (const T*)dpad, (const T*)g1, (const T*)g2, g_nchw, (const T*)r, sb, (const T*)skip, skip_pad, \
-                          prelu_a, (T*)dz, red, dprelu, B, H, W, C, c_real, up, pad););
+                          prelu_a, (T*)dz, red, dprelu, B, H, W, C, c_real, pad););
+#define P2P_BWD_REDUCE(ACT_)                                         \
+  if (up == 2) { P2P_BWD_REDUCE_U(ACT_, 2) }                         \
+  else { P2P_BWD_REDUCE_U(ACT_, 1) }
   switch (act) {
     case P2P_ACT_NONE: P2P_BWD_REDUCE(P2P_ACT_NONE) break;
     case P2P_ACT_RELU: P2P_BWD_REDUCE(P2P_ACT_RELU) break;
@@ -732,6 +788,7 @@ int p2p_bn_act_bwd_reduce(const void* dpad, const void* g1, const void* g2, cons
     default: P2P_REQUIRE(false, "unknown activation");
   }
 #undef P2P_BWD_REDUCE
+#undef P2P_BWD_REDUCE_U
   P2P_LAUNCH_CHECK();
 }
 
