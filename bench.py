@@ -25,7 +25,7 @@ sys.path.insert(0, ROOT)
 
 import torch  # noqa: E402
 
-RES_CONV_DRAM_BYTES = None          # dram bytes of one residual-conv launch from ncu --set full (profiles/); None until re-captured
+RES_CONV_DRAM_BYTES = 18.19e6      # dram__bytes_read.sum + dram__bytes_write.sum of one residual-conv launch (profiles/r01d_ncu_res_fwd.md)
 FLOP_PER_IMG_256 = 173.41e9          # necessary conv FLOPs of one training step per image
 METRIC = "pix2pix 256x256 train images/sec"
 
