@@ -110,7 +110,27 @@ def run_reference(args, rank, world):
                              "sample": f"batch 1 of the {args.batch}-image step, {args.steps} steps, "
                                        f"torch {torch.__version__} fp32 CPU, {cores} threads"},
             "e2e": {"value": ips, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_REAL_STDOUT = None
+
+
+def divert_stdout():
+    """Libraries (NCCL's version banner, the reference-style init prints) write to fd 1; the contract is ONE JSON
+    line on stdout, so fd 1 is pointed at stderr for the duration of the run and the line is written to a saved
+    duplicate of the original stdout."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line):
+    out = _REAL_STDOUT if _REAL_STDOUT is not None else sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
 
 
 def time_dominant_kernel(P, B, S, iters=20):
@@ -282,7 +302,7 @@ def run_ours(args, rank, world, local_rank):
         line["cpu_baseline"] = {"value": n / dt, "unit": "images/s", "cores": cores, "kind": "port",
                                 "sample": f"{n} steps at batch 1 ({S}x{S}) of the oracle (fp32 PyTorch restatement "
                                           f"of train.py:294-390), 2 warm-up steps, {cores} threads"}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def main():
@@ -300,6 +320,7 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    divert_stdout()
     if args.impl == "reference":
         run_reference(args, rank, world)
         return
