@@ -10,6 +10,7 @@ Differences from running the reference loop verbatim on the drop-in modules (all
 """
 from __future__ import annotations
 
+import os
 from typing import Dict, Optional
 
 import torch
@@ -22,9 +23,9 @@ from .optim import FusedAdam
 class GradReducer:
     """Sum-all-reduce of a flat gradient buffer in buckets on the NCCL stream; the mean is folded into Adam
     (grad_scale = 1/world).  Buckets are slices of the flat buffer, launched asynchronously so that the other
-    network's backward overlaps the transfer."""
+    network's backward overlaps the transfer (D's gradients are reduced while G's backward runs)."""
 
-    def __init__(self, group=None, bucket_bytes: int = 8 << 20):
+    def __init__(self, group=None, bucket_bytes: int = 64 << 20):
         import torch.distributed as dist
         self.dist, self.group = dist, group
         self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
@@ -53,7 +54,7 @@ class Pix2PixTrainer:
     """optimizer_g / optimizer_d loop of train.py:241-242, :294-390."""
 
     def __init__(self, net_g, net_d, lr: float = 2e-4, beta1: float = 0.5, process_group=None,
-                 bucket_bytes: int = 8 << 20, cuda_graph: bool = False, graph_warmup: int = 2):
+                 bucket_bytes: int = 64 << 20, cuda_graph: bool = False, graph_warmup: int = 2):
         self.net_g, self.net_d = net_g, net_d
         # cuda_graph=True: the first `graph_warmup` calls of step() run eagerly, the next one records the whole
         # iteration (~650 launches, both backward passes, the all-reduces and both Adam updates) into one CUDA
@@ -66,9 +67,13 @@ class Pix2PixTrainer:
         self.graph_launches = 0          # kernels of libp2p_b200.so recorded in the last captured graph
         self.optimizer_g = FusedAdam(net_g.parameters(), lr=lr, betas=(beta1, 0.999))
         self.optimizer_d = FusedAdam([p for p in net_d.parameters() if p.requires_grad], lr=lr, betas=(beta1, 0.999))
+        if "P2P_BUCKET_MB" in os.environ:                # tuning knob, see DESIGN.md section 5
+            bucket_bytes = int(os.environ["P2P_BUCKET_MB"]) << 20
         self.red_g = GradReducer(process_group, bucket_bytes)
         self.red_d = GradReducer(process_group, bucket_bytes)
         self.world = self.red_g.world
+        # overlap=False: both all-reduces start after both backward passes (nothing competes for SMs)
+        self.overlap = os.environ.get("P2P_DP_OVERLAP", "1") != "0"
         self.optimizer_g.grad_scale = self.optimizer_d.grad_scale = 1.0 / self.world
         self._c_reals = [c[1] for c in net_d._cfg]
         if self.cuda_graph:
@@ -138,13 +143,19 @@ class Pix2PixTrainer:
         loss_g = loss_g_gan + loss_feat + loss_tv                                         # :353,:380
         self.optimizer_g.zero_grad()                                                      # :384
         self.optimizer_d.zero_grad()                                                      # :388 (hoisted: D grads untouched above)
-        loss_g.backward()                                                                 # :385
-        self.red_g.launch(self.optimizer_g.flat_g)        # overlaps with D's backward below
+        # The two backward passes are independent (loss_d sees fake_b detached, the third D pass is frozen), so the
+        # reference's order (:385-390: G backward, G step, D backward, D step) can be permuted without changing a
+        # bit: D's gradients (33 MB, the larger all-reduce) go first and travel while G's backward runs.
         loss_d.backward()                                                                 # :389
-        self.red_d.launch(self.optimizer_d.flat_g)
-        self.red_g.wait()
-        self.optimizer_g.step()                                                           # :386
+        if self.overlap:
+            self.red_d.launch(self.optimizer_d.flat_g)    # overlaps with G's backward below
+        loss_g.backward()                                                                 # :385
+        if not self.overlap:
+            self.red_d.launch(self.optimizer_d.flat_g)
+        self.red_g.launch(self.optimizer_g.flat_g)
         self.red_d.wait()
         self.optimizer_d.step()                                                           # :390
+        self.red_g.wait()
+        self.optimizer_g.step()                                                           # :386
         return {"fake_b": fake_b.detach(), "loss_d": loss_d.detach(), "loss_g_gan": loss_g_gan.detach(),
                 "loss_feat": loss_feat.detach(), "loss_tv": loss_tv.detach(), "loss_g": loss_g.detach()}
