@@ -24,6 +24,11 @@ int conv_fwd_tc(const p2p_conv* c, const void* in, const void* w, const float* b
 int conv_dgrad_tc(const p2p_conv* c, const void* dout, const void* wt, void* din, cudaStream_t st);
 int conv_wgrad_tc(const p2p_conv* c, const void* in, const void* dout, float* dw, cudaStream_t st);
 
+// conv_co1.cu: weight gradient of layers with one real output channel (a memory-bound CUDA-core sweep, chosen
+// under P2P_IMPL_AUTO)
+bool conv_co1_supported(const p2p_conv* c);
+int conv_wgrad_co1(const p2p_conv* c, const void* in, const void* dout, float* dw, int dtype, cudaStream_t st);
+
 static int check_conv(const p2p_conv* c) {
   P2P_REQUIRE(c != nullptr, "null descriptor");
   P2P_REQUIRE(c->N > 0 && c->Hi > 0 && c->Wi > 0 && c->Ho > 0 && c->Wo > 0, "empty tensor");
@@ -97,6 +102,7 @@ int p2p_conv_wgrad(const p2p_conv* c, const void* in, const void* dout, float* d
   cudaStream_t st = as_stream(stream);
   const bool tc_ok = dtype == P2P_BF16 && device_tc() && conv_wgrad_tc_supported(c);
   P2P_REQUIRE(impl != P2P_IMPL_TC || tc_ok, "tcgen05 path does not support this shape / dtype / device");
+  if (impl == P2P_IMPL_AUTO && conv_co1_supported(c)) return conv_wgrad_co1(c, in, dout, dw_acc, dtype, st);
   if (impl != P2P_IMPL_SIMT && tc_ok) return conv_wgrad_tc(c, in, dout, dw_acc, st);
   return conv_wgrad_simt(c, in, dout, dw_acc, dtype, st);
 }

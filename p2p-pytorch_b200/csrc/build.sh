@@ -7,7 +7,7 @@ FLAGS=(-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompil
        -Xptxas -v)
 mkdir -p obj
 pids=()
-for f in api conv_simt conv_tc conv_halo conv_wgrad_tc conv_wgrad_halo elementwise losses_optim weights; do
+for f in api conv_simt conv_tc conv_halo conv_wgrad_tc conv_wgrad_halo conv_co1 elementwise losses_optim weights; do
   if [ ! -f obj/$f.o ] || [ $f.cu -nt obj/$f.o ] || [ common.cuh -nt obj/$f.o ] || [ tc_common.cuh -nt obj/$f.o ] \
      || [ ../../include/p2p_b200.h -nt obj/$f.o ]; then
     ( "$NVCC" "${FLAGS[@]}" -c $f.cu -o obj/$f.o > obj/$f.log 2>&1 || { cat obj/$f.log; exit 1; } ) &

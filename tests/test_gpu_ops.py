@@ -55,6 +55,7 @@ CONV_CASES = [
     ("d_l1_odd",       2, 64, 128, 17, 17, 4, 2, 2),
     ("d_l3",           1, 256, 512, 5, 5, 4, 1, 2),
     ("d_l4",           2, 512, 1, 6, 6, 4, 1, 2),
+    ("d_l4_tiles",     2, 512, 1, 19, 23, 4, 1, 2),
     ("rect_odd",       3, 16, 32, 13, 21, 3, 1, 1),
 ]
 
