@@ -415,53 +415,58 @@ __global__ void __launch_bounds__(256, 4)
   }
 }
 
-// backward pass 2
+// backward pass 2:  dr = scale * (dz - mean(dz) - xhat * mean(dz * xhat))  =  A*dz + Bx*(r - mean) + K  per channel.
+// Four channels per thread, the per-channel coefficients in shared memory (same treatment as pass 1: 32 registers
+// of per-channel state per thread became none).
 template <typename T>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)
     bn_bwd_apply_kernel(const T* __restrict__ dz, const T* __restrict__ r, const float* __restrict__ sb,
                         const double* __restrict__ red, T* __restrict__ dr, float* __restrict__ dbias,
                         float* __restrict__ dgamma, float* __restrict__ dbeta, int64_t pixels, int C, int c_real) {
-  if (blockIdx.x == 0 && dgamma != nullptr && dbeta != nullptr) {      // d gamma = sum dz * xhat, d beta = sum dz
-    for (int c = threadIdx.x; c < c_real; c += blockDim.x) {
+  __shared__ __align__(16) float s_a[512], s_bx[512], s_mean[512], s_k[512];
+  __shared__ float sh[256 * 5];
+  const double inv = 1.0 / (double)pixels;
+  for (int c = threadIdx.x; c < C; c += 256) {
+    const bool real = c < c_real;
+    const float scale = real ? sb[c] : 0.f, istd = sb[3 * C + c];
+    const float m1 = real ? (float)(red[c] * inv) : 0.f, m2 = real ? (float)(red[C + c] * inv) : 0.f;
+    s_a[c] = scale;
+    s_bx[c] = -scale * istd * m2;
+    s_mean[c] = sb[2 * C + c];
+    s_k[c] = -scale * m1;
+    if (blockIdx.x == 0 && real && dgamma != nullptr && dbeta != nullptr) {   // d gamma = sum dz * xhat, d beta = sum dz
       dbeta[c] += (float)red[c];
       dgamma[c] += (float)red[C + c];
     }
   }
-  const int C8 = C >> 3;
-  const int c8 = threadIdx.x % C8, lane_p = threadIdx.x / C8, ppb = 256 / C8;
-  float m1[8], m2[8], sc[8], mean[8], istd[8], sd[8];
-  const double inv = 1.0 / (double)pixels;
-#pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    const int c = c8 * 8 + k;
-    m1[k] = (float)(red[c] * inv);
-    m2[k] = (float)(red[C + c] * inv);
-    sc[k] = sb[c];
-    mean[k] = sb[2 * C + c];
-    istd[k] = sb[3 * C + c];
-    sd[k] = 0.f;
-  }
+  __syncthreads();
+  const int C4 = C >> 2;
+  const int c4 = threadIdx.x % C4, lane_p = threadIdx.x / C4, ppb = 256 / C4;
+  const int c0 = c4 * 4;
+  float sd[4] = {0.f, 0.f, 0.f, 0.f};
   for (int64_t p = (int64_t)blockIdx.x * ppb + lane_p; p < pixels; p += (int64_t)gridDim.x * ppb) {
-    float d[8], rv[8];
-    ld8(dz + (size_t)p * C + c8 * 8, d);
-    ld8(r + (size_t)p * C + c8 * 8, rv);
-#pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const float xh = (rv[k] - mean[k]) * istd[k];
-      const float v = (c8 * 8 + k < c_real) ? sc[k] * (d[k] - m1[k] - xh * m2[k]) : 0.f;
-      d[k] = v;
-      sd[k] += v;
-    }
-    st8(dr + (size_t)p * C + c8 * 8, d);
+    Raw4<T> dd, rr;
+    dd.load(dz + (size_t)p * C + c0);
+    rr.load(r + (size_t)p * C + c0);
+    const float4 a = *reinterpret_cast<const float4*>(s_a + c0), bx = *reinterpret_cast<const float4*>(s_bx + c0);
+    const float4 mu = *reinterpret_cast<const float4*>(s_mean + c0), kk = *reinterpret_cast<const float4*>(s_k + c0);
+    float d[4], rv[4];
+    dd.get(d);
+    rr.get(rv);
+    d[0] = fmaf(a.x, d[0], fmaf(bx.x, rv[0] - mu.x, kk.x));
+    d[1] = fmaf(a.y, d[1], fmaf(bx.y, rv[1] - mu.y, kk.y));
+    d[2] = fmaf(a.z, d[2], fmaf(bx.z, rv[2] - mu.z, kk.z));
+    d[3] = fmaf(a.w, d[3], fmaf(bx.w, rv[3] - mu.w, kk.w));
+    sd[0] += d[0]; sd[1] += d[1]; sd[2] += d[2]; sd[3] += d[3];
+    Raw4<T>::store(dr + (size_t)p * C + c0, d);
   }
   if (dbias != nullptr) {
-    __shared__ float sh[8][256];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) sh[k][threadIdx.x] = sd[k];
+    for (int k = 0; k < 4; ++k) sh[threadIdx.x * 5 + k] = sd[k];
     __syncthreads();
     for (int c = threadIdx.x; c < c_real; c += 256) {
       float acc = 0.f;
-      for (int l = 0; l < ppb; ++l) acc += sh[c & 7][l * C8 + (c >> 3)];
+      for (int l = 0; l < ppb; ++l) acc += sh[(l * C4 + (c >> 2)) * 5 + (c & 3)];
       atomicAdd(dbias + c, acc);
     }
   }
@@ -769,9 +774,7 @@ int p2p_bn_act_bwd_reduce(const void* dpad, const void* g1, const void* g2, cons
   P2P_REQUIRE(256 % (C / 4) == 0, "C must be 16, 32, 64, 128, 256 or 512");
   const int ppb = 256 / (C / 4);
   const int64_t pixels = (int64_t)B * H * W;
-  static const int bps = getenv("P2P_RED_BPS") ? atoi(getenv("P2P_RED_BPS")) : 4;
-  const int64_t want = (pixels + ppb - 1) / ppb;
-  const int grid = (int)(want < (int64_t)kSMs * bps ? want : (int64_t)kSMs * bps);
+  const int grid = red_ew_grid(pixels, ppb);       // 4 resident blocks per SM
 #define P2P_BWD_REDUCE_U(ACT_, UP_)                                                                              \
   P2P_DISPATCH(dtype, bn_act_bwd_reduce_kernel<T, ACT_, UP_><<<grid, 256, 0, as_stream(stream)>>>(               \
                           (const T*)dpad, (const T*)g1, (const T*)g2, g_nchw, (const T*)r, sb, (const T*)skip, skip_pad, \
@@ -795,8 +798,8 @@ int p2p_bn_act_bwd_reduce(const void* dpad, const void* g1, const void* g2, cons
 int p2p_bn_bwd_apply(const void* dz, const void* r, const float* sb, const double* red, void* dr, float* dgamma,
                      float* dbeta, float* dbias, int64_t pixels, int C, int c_real, int dtype, void* stream) {
   P2P_REQUIRE(dz && r && sb && red && dr, "null pointer");
-  P2P_REQUIRE(C % 16 == 0 && C <= 512, "C must be a multiple of 16, <= 512");
-  const int ppb = 256 / (C / 8);
+  P2P_REQUIRE(C % 16 == 0 && C <= 512 && 256 % (C / 4) == 0, "C must be 16, 32, 64, 128, 256 or 512");
+  const int ppb = 256 / (C / 4);
   P2P_DISPATCH(dtype, bn_bwd_apply_kernel<T><<<red_ew_grid(pixels, ppb), 256, 0, as_stream(stream)>>>(
                           (const T*)dz, (const T*)r, sb, red, (T*)dr, dbias, dgamma, dbeta, pixels, C, c_real););
   P2P_LAUNCH_CHECK();
