@@ -699,6 +699,36 @@ static inline int red_ew_grid(int64_t pixels, int ppb) {
   return (int)(g < 1 ? 1 : (g > cap ? cap : g));
 }
 
+// =================================================================================================
+// Convolution with one output channel as "1x1 convolution with one output column per filter tap" + this gather:
+//   out[n, oy, ox, 0] = bias + sum_{ky,kx} t[n, oy + ky - pad, ox + kx - pad, ky*kw + kx]      (zero outside)
+// t = the input map times the [taps x Ci] filter, one value per (input pixel, tap).  Channels 1..15 of out are 0.
+// =================================================================================================
+template <typename T>
+__global__ void __launch_bounds__(256) tap_gather_sum_kernel(const T* __restrict__ t, const float* __restrict__ bias,
+                                                             T* __restrict__ out, int N, int Hi, int Wi, int Ho, int Wo,
+                                                             int kh, int kw, int pad, int act) {
+  const int64_t total = (int64_t)N * Ho * Wo;
+  const float b0 = bias != nullptr ? bias[0] : 0.f;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int ox = (int)(i % Wo), oy = (int)((i / Wo) % Ho), n = (int)(i / ((int64_t)Wo * Ho));
+    float acc = b0;
+    for (int ky = 0; ky < kh; ++ky) {
+      const int iy = oy + ky - pad;
+      if (iy < 0 || iy >= Hi) continue;
+      for (int kx = 0; kx < kw; ++kx) {
+        const int ix = ox + kx - pad;
+        if (ix < 0 || ix >= Wi) continue;
+        acc += ldf(t + (((size_t)n * Hi + iy) * Wi + ix) * 16 + ky * kw + kx);
+      }
+    }
+    if (act == P2P_ACT_LRELU) acc = fmaxf(acc, 0.2f * acc);
+    float v[8] = {acc, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, z[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    st8(out + (size_t)i * 16, v);
+    st8(out + (size_t)i * 16 + 8, z);
+  }
+}
+
 }  // namespace p2p
 
 using namespace p2p;
@@ -859,6 +889,17 @@ int p2p_act_bwd(const void* out, const void* g_a, const void* g_b, void* dz, flo
   const int ppb = 256 / (C / 8);
   P2P_DISPATCH(dtype, act_bwd_kernel<T><<<red_ew_grid(pixels, ppb), 256, 0, as_stream(stream)>>>(
                           (const T*)out, (const T*)g_a, (const T*)g_b, (T*)dz, dbias, pixels, C, c_real, act););
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_tap_gather_sum(const void* t, const float* bias, void* out, int N, int Hi, int Wi, int Ho, int Wo, int kh,
+                       int kw, int pad, int act, int dtype, void* stream) {
+  P2P_REQUIRE(t && out && N > 0 && kh > 0 && kw > 0 && kh * kw <= 16, "bad arguments");
+  P2P_REQUIRE(Ho == Hi + 2 * pad - kh + 1 && Wo == Wi + 2 * pad - kw + 1, "stride-1 geometry expected");
+  P2P_REQUIRE(act == P2P_ACT_NONE || act == P2P_ACT_LRELU, "epilogue activation must be none or leaky relu");
+  const int64_t total = (int64_t)N * Ho * Wo;
+  P2P_DISPATCH(dtype, tap_gather_sum_kernel<T><<<ew_grid(total), 256, 0, as_stream(stream)>>>(
+                          (const T*)t, bias, (T*)out, N, Hi, Wi, Ho, Wo, kh, kw, pad, act););
   P2P_LAUNCH_CHECK();
 }
 

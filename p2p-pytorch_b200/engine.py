@@ -92,6 +92,18 @@ class ConvPlan:
                          self.Ci, self.k, self.k)
 
     def fwd(self, x, bias, out, stats):
+        d = self.desc
+        if (self.cout_real == 1 and self.stride == 1 and self.k * self.k <= 16 and stats is None
+                and _state["impl"] == L.IMPL_AUTO and x.dtype == torch.bfloat16):
+            # one real output channel (D's last layer): a 1x1 convolution with one output column per filter tap -- the
+            # [taps x Ci] filter row IS that 1x1 weight matrix -- reads the input once; then a 16-tap gather-sum
+            t = _empty((d.N, d.Hi, d.Wi, 16), x.dtype, x.device)
+            d1 = Conv(d.N, d.Hi, d.Wi, d.Ci, d.Hi, d.Wi, 16, 1, 1, 1, 0, 16, self.cin_real, L.ACT_NONE)
+            call("p2p_conv_fwd", C.byref(d1), ptr(x), ptr(self.wp), None, ptr(t), None, L.dtype_code(x.dtype),
+                 _state["impl"])
+            call("p2p_tap_gather_sum", ptr(t), ptr(bias), ptr(out), d.N, d.Hi, d.Wi, d.Ho, d.Wo, self.k, self.k,
+                 self.pad, self.act, L.dtype_code(x.dtype))
+            return
         call("p2p_conv_fwd", C.byref(self.desc), ptr(x), ptr(self.wp), ptr(bias), ptr(out), ptr(stats),
              L.dtype_code(x.dtype), _state["impl"])
 

@@ -89,6 +89,11 @@ def _conv_case(case, dt, impl, tol):
         st_ref = torch.stack([got.sum((0, 2, 3)), (got * got).sum((0, 2, 3))]).double()
         st = stats.view(2, Co)[:, :cout]
         assert relerr(st, st_ref) <= max(tol, 1e-5) * 5, f"{name} stats"
+        # without statistics (the discriminator's use): one-channel layers take the 1x1 + tap-gather route
+        out2 = torch.full_like(out, 3.0)
+        plan.fwd(xs, bias, out2, None)
+        assert relerr(from_stored(out2, cout), ref) <= tol, f"{name} fwd without stats"
+        assert out2[..., cout:].abs().max().item() == 0 if Co > cout else True
         # backward
         go = torch.randn(ref.shape, generator=g).to(DEV)
         gos = to_stored(go, Co, dt)
