@@ -201,6 +201,11 @@ int p2p_act_bwd(const void* out, const void* g_a, const void* g_b, void* dz, flo
  * instead of once per tap (46 -> 12 us for the 35x35 map at batch 16). */
 int p2p_tap_gather_sum(const void* t, const float* bias, void* out, int N, int Hi, int Wi, int Ho, int Wo, int kh,
                        int kw, int pad, int act, int dtype, void* stream);
+/* The data-gradient counterpart: a[n,iy,ix,ky*kw+kx] = dy[n, iy+pad-ky, ix+pad-kx, 0] (zero outside; dy and a have
+ * 16 stored channels).  p2p_conv_fwd of `a` with the [Ci x taps] filter matrix (kh = kw = 1, 16 input channels) is
+ * the gradient w.r.t. the input of the one-output-channel convolution. */
+int p2p_tap_scatter(const void* dy, void* a, int N, int Hi, int Wi, int Ho, int Wo, int kh, int kw, int pad, int dtype,
+                    void* stream);
 /* stored map [B,H,W,C] dtype <-> NCHW fp32 [B,c_real,H,W] (drop-in API edge). */
 int p2p_nhwc_to_nchw(const void* in, float* out, int B, int H, int W, int C, int c_real, int dtype, void* stream);
 int p2p_nchw_to_nhwc(const float* in, void* out, int B, int H, int W, int C, int c_real, int dtype, void* stream);

@@ -729,6 +729,28 @@ __global__ void __launch_bounds__(256) tap_gather_sum_kernel(const T* __restrict
   }
 }
 
+// the data-gradient counterpart: a[n, iy, ix, ky*kw + kx] = dy[n, iy + pad - ky, ix + pad - kx, 0]  (zero outside);
+// a 1x1 convolution of `a` with the [Ci x taps] filter matrix is then the gradient w.r.t. the layer input
+template <typename T>
+__global__ void __launch_bounds__(256) tap_scatter_kernel(const T* __restrict__ dy, T* __restrict__ a, int N, int Hi,
+                                                          int Wi, int Ho, int Wo, int kh, int kw, int pad) {
+  const int64_t total = (int64_t)N * Hi * Wi;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int ix = (int)(i % Wi), iy = (int)((i / Wi) % Hi), n = (int)(i / ((int64_t)Wi * Hi));
+    float v[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) v[k] = 0.f;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+      const int ky = k / kw, kx = k - ky * kw;
+      const int oy = iy + pad - ky, ox = ix + pad - kx;
+      if (k < kh * kw && oy >= 0 && oy < Ho && ox >= 0 && ox < Wo) v[k] = ldf(dy + (((size_t)n * Ho + oy) * Wo + ox) * 16);
+    }
+    st8(a + (size_t)i * 16, v);
+    st8(a + (size_t)i * 16 + 8, v + 8);
+  }
+}
+
 }  // namespace p2p
 
 using namespace p2p;
@@ -900,6 +922,16 @@ int p2p_tap_gather_sum(const void* t, const float* bias, void* out, int N, int H
   const int64_t total = (int64_t)N * Ho * Wo;
   P2P_DISPATCH(dtype, tap_gather_sum_kernel<T><<<ew_grid(total), 256, 0, as_stream(stream)>>>(
                           (const T*)t, bias, (T*)out, N, Hi, Wi, Ho, Wo, kh, kw, pad, act););
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_tap_scatter(const void* dy, void* a, int N, int Hi, int Wi, int Ho, int Wo, int kh, int kw, int pad, int dtype,
+                    void* stream) {
+  P2P_REQUIRE(dy && a && N > 0 && kh > 0 && kw > 0 && kh * kw <= 16, "bad arguments");
+  P2P_REQUIRE(Ho == Hi + 2 * pad - kh + 1 && Wo == Wi + 2 * pad - kw + 1, "stride-1 geometry expected");
+  const int64_t total = (int64_t)N * Hi * Wi;
+  P2P_DISPATCH(dtype, tap_scatter_kernel<T><<<ew_grid(total), 256, 0, as_stream(stream)>>>((const T*)dy, (T*)a, N, Hi, Wi,
+                                                                                          Ho, Wo, kh, kw, pad););
   P2P_LAUNCH_CHECK();
 }
 

@@ -74,7 +74,12 @@ class ConvPlan:
         self.Co = pad16(cout_real)
         self.desc = Conv(N, Hi, Wi, Ci, self.Ho, self.Wo, self.Co, k, k, stride, pad, cout_real, cin_real, act)
         self.cin_real, self.cout_real, self.Ci, self.act = cin_real, cout_real, Ci, act
-        self.wp = self.wt = None
+        self.wp = self.wt = self.w1x1 = None
+
+    def one_channel(self, dt) -> bool:
+        """D's last layer (512 -> 1): forward and data-gradient run as 1x1 convolutions over the filter taps."""
+        return (self.cout_real == 1 and self.stride == 1 and self.k * self.k <= 16
+                and _state["impl"] == L.IMPL_AUTO and dt == torch.bfloat16)
 
     def pack(self, weight, sigma, dt, want_wt=True):
         dev = weight.device
@@ -82,6 +87,8 @@ class ConvPlan:
         self.wt = _empty((self.Ci, self.k, self.k, self.Co), dt, dev) if want_wt else None
         call("p2p_pack_weights", ptr(weight), ptr(sigma), ptr(self.wp), ptr(self.wt), self.cout_real, self.cin_real,
              self.Co, self.Ci, self.k, self.k, L.dtype_code(dt))
+        for job in self.extra_pack_jobs(weight, sigma, dt):
+            L.call_multi("p2p_pack_weights_multi", [job], L.dtype_code(dt))
 
     def pack_job(self, weight, sigma, dt, want_wt=True) -> L.PackJob:
         """Allocate the packed buffers and describe the packing for one batched p2p_pack_weights_multi launch."""
@@ -91,10 +98,17 @@ class ConvPlan:
         return L.PackJob(ptr(weight), ptr(sigma), ptr(self.wp), ptr(self.wt), self.cout_real, self.cin_real, self.Co,
                          self.Ci, self.k, self.k)
 
+    def extra_pack_jobs(self, weight, sigma, dt):
+        """One-channel layers also keep the filter as a [Ci][taps -> 16] matrix: the PyTorch weight [1][ci][kh][kw]
+        read as a 1x1 filter bank with ci outputs and kh*kw inputs (used by dgrad)."""
+        if not self.one_channel(dt):
+            return []
+        self.w1x1 = _empty((self.Ci, 1, 1, 16), dt, weight.device)
+        return [L.PackJob(ptr(weight), ptr(sigma), ptr(self.w1x1), None, self.cin_real, self.k * self.k, self.Ci, 16, 1, 1)]
+
     def fwd(self, x, bias, out, stats):
         d = self.desc
-        if (self.cout_real == 1 and self.stride == 1 and self.k * self.k <= 16 and stats is None
-                and _state["impl"] == L.IMPL_AUTO and x.dtype == torch.bfloat16):
+        if stats is None and self.one_channel(x.dtype):
             # one real output channel (D's last layer): a 1x1 convolution with one output column per filter tap -- the
             # [taps x Ci] filter row IS that 1x1 weight matrix -- reads the input once; then a 16-tap gather-sum
             t = _empty((d.N, d.Hi, d.Wi, 16), x.dtype, x.device)
@@ -108,6 +122,15 @@ class ConvPlan:
              L.dtype_code(x.dtype), _state["impl"])
 
     def dgrad(self, dout, din):
+        d = self.desc
+        if self.w1x1 is not None and self.one_channel(dout.dtype):
+            a = _empty((d.N, d.Hi, d.Wi, 16), dout.dtype, dout.device)
+            call("p2p_tap_scatter", ptr(dout), ptr(a), d.N, d.Hi, d.Wi, d.Ho, d.Wo, self.k, self.k, self.pad,
+                 L.dtype_code(dout.dtype))
+            d1 = Conv(d.N, d.Hi, d.Wi, 16, d.Hi, d.Wi, d.Ci, 1, 1, 1, 0, self.cin_real, self.k * self.k, L.ACT_NONE)
+            call("p2p_conv_fwd", C.byref(d1), ptr(a), ptr(self.w1x1), None, ptr(din), None, L.dtype_code(dout.dtype),
+                 _state["impl"])
+            return
         call("p2p_conv_dgrad", C.byref(self.desc), ptr(dout), ptr(self.wt), ptr(din), L.dtype_code(dout.dtype),
              _state["impl"])
 
@@ -405,6 +428,7 @@ class DiscriminatorFunction(torch.autograd.Function):
             for j, (_cin, cout, _stride, _sn) in enumerate(layer_cfg):
                 pk = ConvPlan(1, 4, 4, pad16(ci), ci, cout, 4, 1, 2)
                 jobs.append(pk.pack_job(params[2 * (sc * nl + j)], sig_of.get((sc, j)), dt))
+                jobs += pk.extra_pack_jobs(params[2 * (sc * nl + j)], sig_of.get((sc, j)), dt)
                 packs[(sc, j)] = pk
                 ci = cout
         L.call_multi("p2p_pack_weights_multi", jobs, dc)
@@ -418,7 +442,7 @@ class DiscriminatorFunction(torch.autograd.Function):
                 wgt, bias = params[2 * (sc * nl + j)], params[2 * (sc * nl + j) + 1]
                 act = L.ACT_LRELU if j != nl - 1 else L.ACT_NONE
                 plan = ConvPlan(B, cur.shape[1], cur.shape[2], cur.shape[3], cin_real, cout, 4, stride, 2, act)
-                plan.wp, plan.wt = packs[(sc, j)].wp, packs[(sc, j)].wt
+                plan.wp, plan.wt, plan.w1x1 = packs[(sc, j)].wp, packs[(sc, j)].wt, packs[(sc, j)].w1x1
                 o = _empty((B, plan.Ho, plan.Wo, plan.Co), dt, dev)
                 plan.fwd(cur, bias, o, None)
                 plans.append(plan)
