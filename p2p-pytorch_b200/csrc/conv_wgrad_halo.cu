@@ -41,6 +41,11 @@ struct WhParams {
   int stages, stage_bytes;
   int blocks_w, blocks_h, n_img, blocks_per_split;
   int Ci, Co;
+  // "ky on the B side" mode (Ci, Co <= 64): the M tiles chain only the kx taps; the N dimension of one MMA is
+  // (g_ky filter rows) x Co, read from a dy tile with a (g_ky - 1)-line halo above the block -- atom j of the B
+  // operand is the same 16-pixel line of dy one line further down (LBO = one line), i.e. filter row ky_hi - j.
+  // blockIdx.y then selects the group of filter rows instead of an output-channel tile.
+  int ky_b, g_ky, kh, kw, pad, HHy;
   float* dw;
   WhTile tiles[kWhMaxTiles];
 };
@@ -56,10 +61,12 @@ __global__ void __launch_bounds__(192, 1)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int rbx = p.cin_blk * 2, rby = p.co_blk * 2;
   const int x_total = p.n_chunks * p.x_bytes;
-  const int dy_box = kWhRows * kWhCols * rby;
+  const int dy_box = (p.ky_b ? p.HHy : kWhRows) * kWhCols * rby;
   const int mt0 = blockIdx.x * p.mt;
   const int my_mt = min(p.mt, p.n_tiles_m - mt0);
-  const int co0 = blockIdx.y * p.n_cols;
+  const int co0 = p.ky_b ? 0 : blockIdx.y * p.n_cols;
+  // ky_b: highest filter row of this CTA's group (atom 0); rows ky_hi - j, j = 0 .. g_ky-1 (negative = padding)
+  const int ky_hi = p.ky_b ? min(p.kh, (int)(blockIdx.y + 1) * p.g_ky) - 1 : 0;
   const int total_blocks = p.n_img * p.blocks_w * p.blocks_h;
   const int t_beg = blockIdx.z * p.blocks_per_split;
   const int t_end = min(total_blocks, t_beg + p.blocks_per_split);
@@ -98,8 +105,13 @@ __global__ void __launch_bounds__(192, 1)
         for (int c = 0; c < p.n_chunks; ++c)
           tma_load_4d(sx + c * p.x_bytes, &map_x, &full_bar[stage], c * p.cin_blk, ox0 + p.min_dw, oy0 + p.min_dh, n);
         uint8_t* sy = sx + x_total;
-        for (int b = 0; b < p.b_boxes; ++b)
-          tma_load_4d(sy + b * dy_box, &map_dy, &full_bar[stage], co0 + b * p.co_blk, ox0, oy0, n);
+        if (p.ky_b) {
+          // block rows are INPUT rows iy = oy0 + min_dh ..; dy row of atom j at block row y: iy + pad - (ky_hi - j)
+          tma_load_4d(sy, &map_dy, &full_bar[stage], 0, ox0, oy0 + p.min_dh + p.pad - ky_hi, n);
+        } else {
+          for (int b = 0; b < p.b_boxes; ++b)
+            tma_load_4d(sy + b * dy_box, &map_dy, &full_bar[stage], co0 + b * p.co_blk, ox0, oy0, n);
+        }
         if (++stage == p.stages) { stage = 0; phase ^= 1; }
       }
     }
@@ -110,7 +122,7 @@ __global__ void __launch_bounds__(192, 1)
     const uint32_t a_hi = desc_hi(8 * rbx, rbx), b_hi = desc_hi(8 * rby, rby);
     const uint32_t a_ystep = (uint32_t)(p.HWx * rbx) >> 4;          // next block row: one halo line down
     const uint32_t b_ystep = (uint32_t)(kWhCols * rby) >> 4;        // next block row: 16 dy rows down
-    const uint32_t b_lbo = ((uint32_t)dy_box >> 4) << 16;
+    const uint32_t b_lbo = ((uint32_t)(p.ky_b ? kWhCols * rby : dy_box) >> 4) << 16;
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0, first = 0;
@@ -142,13 +154,19 @@ __global__ void __launch_bounds__(192, 1)
     mbar_wait(&tmem_full_bar, 0);
     tc_fence_after();
     for (int m = 0; m < my_mt; ++m) {
-      const int tap = p.tiles[mt0 + m].tap[atom];
+      const int tap = p.tiles[mt0 + m].tap[atom];      // ky_b: the kx of this atom (filter row comes from the column)
       const int c0 = p.tiles[mt0 + m].c0[atom];
-      float* dst = (tap >= 0) ? p.dw + ((int64_t)tap * p.Ci + c0 + cin) * p.Co + co0 : nullptr;
+      float* dst0 = (tap >= 0) ? p.dw + ((int64_t)tap * p.Ci + c0 + cin) * p.Co + co0 : nullptr;
       for (int c = 0; c < p.n_cols; c += 16) {
         uint32_t v[16];
         tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(m * p.n_cols + c), v);
         tmem_ld_wait();
+        float* dst = dst0;
+        if (p.ky_b) {
+          const int ky = ky_hi - c / p.Co;               // 16-column chunks never straddle a filter row (Co % 16 == 0)
+          const bool mine = ky >= 0 && ky > ky_hi - p.g_ky && ky >= (int)blockIdx.y * p.g_ky;
+          dst = (tap >= 0 && mine) ? p.dw + ((int64_t)(ky * p.kw + tap) * p.Ci + c0 + cin) * p.Co + (c % p.Co) - c : nullptr;
+        }
         if (dst != nullptr) {
 #pragma unroll
           for (int j = 0; j < 16; j += 4) {
@@ -184,7 +202,18 @@ int conv_wgrad_halo(const p2p_conv* c, const void* in, const void* dout, float* 
     for (int j = 0; j < 8; ++j) { t.tap[j] = -1; t.c0[j] = 0; }
     return t;
   };
-  if (c->Ci == 128) {
+  static const bool no_kyb = getenv("P2P_NO_WGRAD_KYB") != nullptr && atoi(getenv("P2P_NO_WGRAD_KYB")) != 0;
+  const bool ky_b = !no_kyb && c->Ci <= 64 && c->Co <= 64 && c->kh > 1;
+  if (ky_b) {
+    // M tiles chain the kx taps only; filter rows ride on the N dimension (see WhParams)
+    for (int kx = 0; kx < c->kw; kx += apt) {
+      if (nt >= kWhMaxTiles) return -2;
+      WhTile& t = new_tile();
+      t.lo_const = (uint32_t)kx | 0x40000000u;                             // kx chain starting at column kx, row 0
+      for (int j = 0; j < apt && kx + j < c->kw; ++j) t.tap[j] = (int16_t)(kx + j);
+      if (kx + apt > c->kw) extra_w = kx + apt - c->kw;
+    }
+  } else if (c->Ci == 128) {
     // one tile per tap: atoms = the two 64-channel halves, one halo buffer apart (filled in below)
     for (int ky = 0; ky < c->kh; ++ky)
       for (int kx = 0; kx < c->kw; ++kx) {
@@ -213,14 +242,22 @@ int conv_wgrad_halo(const p2p_conv* c, const void* in, const void* dout, float* 
         if (ky + apt > c->kh) extra_h = extra_h > ky + apt - c->kh ? extra_h : ky + apt - c->kh;
       }
   }
-  (void)extra_w;
   p.n_tiles_m = nt;
   p.cin_blk = cin_blk;
   p.n_chunks = n_chunks;
   p.min_dh = -c->pad;
   p.min_dw = -c->pad;
-  p.HWx = kWhCols + c->kw - 1;
-  p.HHx = kWhRows + c->kh - 1 + extra_h;
+  p.HWx = kWhCols + c->kw - 1 + extra_w;
+  p.HHx = ky_b ? kWhRows : kWhRows + c->kh - 1 + extra_h;
+  p.ky_b = ky_b ? 1 : 0;
+  p.kh = c->kh; p.kw = c->kw; p.pad = c->pad;
+  int ky_groups = 1;
+  if (ky_b) {
+    const int max_rows = 256 / c->Co;                                     // filter rows that fit one N <= 256
+    ky_groups = (c->kh + max_rows - 1) / max_rows;
+    p.g_ky = (c->kh + ky_groups - 1) / ky_groups;
+    p.HHy = kWhRows + p.g_ky - 1;
+  }
   p.x_bytes = ((p.HHx * p.HWx * rbx + 1023) / 1024) * 1024;
   for (int i = 0; i < nt; ++i) {
     const uint32_t code = p.tiles[i].lo_const;
@@ -233,24 +270,25 @@ int conv_wgrad_halo(const p2p_conv* c, const void* in, const void* dout, float* 
     if ((lbo_bytes >> 4) > 0x3FFF) return -2;
   }
   p.co_blk = c->Co >= 64 ? 64 : c->Co;
-  p.n_cols = c->Co >= 256 ? 256 : c->Co;
-  p.b_boxes = p.n_cols / p.co_blk;
+  p.n_cols = ky_b ? p.g_ky * c->Co : (c->Co >= 256 ? 256 : c->Co);
+  p.b_boxes = ky_b ? 1 : p.n_cols / p.co_blk;
   int mt_max = 512 / p.n_cols;
   const int groups = (nt + mt_max - 1) / mt_max;
   p.mt = (nt + groups - 1) / groups;
-  p.stage_bytes = n_chunks * p.x_bytes + ((p.b_boxes * kWhRows * kWhCols * p.co_blk * 2 + 1023) / 1024) * 1024;
+  p.stage_bytes = n_chunks * p.x_bytes +
+                  ((p.b_boxes * (ky_b ? p.HHy : kWhRows) * kWhCols * p.co_blk * 2 + 1023) / 1024) * 1024;
   int stages = (216 * 1024) / p.stage_bytes;
   stages = stages > 6 ? 6 : stages;
   if (stages < 2) return -2;
   p.stages = stages;
   p.blocks_w = (c->Wo + kWhCols - 1) / kWhCols;
-  p.blocks_h = (c->Ho + kWhRows - 1) / kWhRows;
+  p.blocks_h = ((ky_b ? c->Ho + c->kh - 1 : c->Ho) + kWhRows - 1) / kWhRows;   // ky_b: blocks of INPUT rows
   p.n_img = c->N;
   p.Ci = c->Ci;
   p.Co = c->Co;
   p.dw = dw;
   const int total_blocks = c->N * p.blocks_w * p.blocks_h;
-  const int n_tiles_n = c->Co / p.n_cols;
+  const int n_tiles_n = ky_b ? ky_groups : c->Co / p.n_cols;
   int splits = kSMs / (groups * n_tiles_n);
   if (splits < 1) splits = 1;
   if (splits > total_blocks) splits = total_blocks;
@@ -268,7 +306,7 @@ int conv_wgrad_halo(const p2p_conv* c, const void* in, const void* dout, float* 
   {
     const uint64_t dims[4] = {(uint64_t)c->Co, (uint64_t)c->Wo, (uint64_t)c->Ho, (uint64_t)c->N};
     const uint64_t strides[3] = {(uint64_t)c->Co * 2, (uint64_t)c->Wo * c->Co * 2, (uint64_t)c->Ho * c->Wo * c->Co * 2};
-    const uint32_t box[4] = {(uint32_t)p.co_blk, (uint32_t)kWhCols, (uint32_t)kWhRows, 1};
+    const uint32_t box[4] = {(uint32_t)p.co_blk, (uint32_t)kWhCols, (uint32_t)(ky_b ? p.HHy : kWhRows), 1};
     const uint32_t es[4] = {1, 1, 1, 1};
     if (int e = make_map_bf16(&my, dout, 4, dims, strides, box, es, p.co_blk * 2)) return e;
   }
