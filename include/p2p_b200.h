@@ -206,6 +206,17 @@ int p2p_tap_gather_sum(const void* t, const float* bias, void* out, int N, int H
  * the gradient w.r.t. the input of the one-output-channel convolution. */
 int p2p_tap_scatter(const void* dy, void* a, int N, int Hi, int Wi, int Ho, int Wo, int kh, int kw, int pad, int dtype,
                     void* stream);
+/* Wide filters with very few output channels (ExpandNetwork's last layer: 9x9, 32 -> 3, networks.py:487): the layer
+ * runs as a (kh x 1) convolution with kw*co_real "fat" output channels -- weights W'[(kx*co_real+co)][ky][0][ci] =
+ * w[co][ci][ky][kx], p2p_conv_fwd with kw = 1 -- followed by the horizontal gather
+ *   out[n,y,x,co] = bias[co] + sum_kx t[n, y, x+kx, kx*co_real+co]      t: [N,H,Wt=Wo+kw-1,Ct], out: [N,H,Wo,Co];
+ * the data-gradient is the adjoint scatter  a[n,y,xa,kx*co_real+co] = dy[n,y,xa-kx,co]  (a: [N,H,Wa=Wo+kw-1,Ca])
+ * followed by p2p_conv_dgrad of the fat convolution.  Nine times fewer tensor-core instructions than one
+ * 16-column MMA per filter tap. */
+int p2p_kx_gather_sum(const void* t, const float* bias, void* out, int N, int H, int Wt, int Wo, int kw, int co_real,
+                      int Ct, int Co, int dtype, void* stream);
+int p2p_kx_scatter(const void* dy, void* a, int N, int H, int Wo, int Wa, int kw, int co_real, int Cs, int Ca, int dtype,
+                   void* stream);
 /* stored map [B,H,W,C] dtype <-> NCHW fp32 [B,c_real,H,W] (drop-in API edge). */
 int p2p_nhwc_to_nchw(const void* in, float* out, int B, int H, int W, int C, int c_real, int dtype, void* stream);
 int p2p_nchw_to_nhwc(const float* in, void* out, int B, int H, int W, int C, int c_real, int dtype, void* stream);

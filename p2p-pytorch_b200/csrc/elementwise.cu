@@ -751,6 +751,74 @@ __global__ void __launch_bounds__(256) tap_scatter_kernel(const T* __restrict__ 
   }
 }
 
+// =================================================================================================
+// Wide filters with very few output channels (the generator's last layer, 9x9, 32 -> 3): the convolution runs as a
+// kh x 1 convolution with kw * co "fat" output channels (one MMA column per (kx, co) pair instead of 16 columns
+// per tap), and these two kernels are the horizontal part:
+//   gather:   out[n, y, x, co] = bias[co] + sum_kx t[n, y, x + kx, kx * co_real + co]
+//   scatter:  a[n, y, xa, kx * co_real + co] = dy[n, y, xa - kx, co]                    (the adjoint, for dgrad)
+// =================================================================================================
+template <typename T>
+__global__ void __launch_bounds__(256) kx_gather_sum_kernel(const T* __restrict__ t, const float* __restrict__ bias,
+                                                            T* __restrict__ out, int H, int Wt, int Wo, int kw,
+                                                            int co_real, int Ct, int Co) {
+  extern __shared__ __align__(16) uint32_t s_t[];          // [(256 + kw - 1) pixels][Ct/2 + 1 words]
+  const int pitch = Ct / 2 + 1;
+  const int x0 = blockIdx.x * 256, y = blockIdx.y, n = blockIdx.z;
+  const int npix = min(256, Wo - x0) + kw - 1;
+  const uint32_t* src = reinterpret_cast<const uint32_t*>(t + (((size_t)n * H + y) * Wt + x0) * Ct);   // bf16 pairs
+  if (sizeof(T) == 2) {
+    for (int e = threadIdx.x; e < npix * (Ct / 2); e += 256) s_t[(e / (Ct / 2)) * pitch + e % (Ct / 2)] = src[e];
+  }
+  __syncthreads();
+  const int x = x0 + threadIdx.x;
+  if (x >= Wo) return;
+  float acc[8];
+#pragma unroll
+  for (int c = 0; c < 8; ++c) acc[c] = (c < co_real && bias != nullptr) ? bias[c] : 0.f;
+  for (int kx = 0; kx < kw; ++kx) {
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      if (c >= co_real) break;
+      const int ch = kx * co_real + c;
+      float v;
+      if (sizeof(T) == 2) {
+        const uint32_t w = s_t[(threadIdx.x + kx) * pitch + (ch >> 1)];
+        v = __uint_as_float((ch & 1) ? (w & 0xffff0000u) : (w << 16));
+      } else {
+        v = ldf(t + (((size_t)n * H + y) * Wt + x + kx) * Ct + ch);
+      }
+      acc[c] += v;
+    }
+  }
+  T* o = out + (((size_t)n * H + y) * Wo + x) * Co;
+  for (int c0 = 0; c0 < Co; c0 += 8) {
+    float v[8];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) v[c] = (c0 == 0 && c < co_real) ? acc[c] : 0.f;
+    st8(o + c0, v);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) kx_scatter_kernel(const T* __restrict__ dy, T* __restrict__ a, int N, int H, int Wo,
+                                                         int Wa, int kw, int co_real, int Cs, int Ca) {
+  const int64_t total = (int64_t)N * H * Wa * (Ca / 8);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % (Ca / 8));
+    int64_t q = i / (Ca / 8);
+    const int xa = (int)(q % Wa); q /= Wa;               // q = n * H + y
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int ch = c8 * 8 + j, kx = ch / co_real, co = ch - kx * co_real;
+      const int x = xa - kx;
+      v[j] = (kx < kw && x >= 0 && x < Wo) ? ldf(dy + ((size_t)q * Wo + x) * Cs + co) : 0.f;
+    }
+    st8(a + (size_t)i * 8, v);
+  }
+}
+
 }  // namespace p2p
 
 using namespace p2p;
@@ -932,6 +1000,29 @@ int p2p_tap_scatter(const void* dy, void* a, int N, int Hi, int Wi, int Ho, int 
   const int64_t total = (int64_t)N * Hi * Wi;
   P2P_DISPATCH(dtype, tap_scatter_kernel<T><<<ew_grid(total), 256, 0, as_stream(stream)>>>((const T*)dy, (T*)a, N, Hi, Wi,
                                                                                           Ho, Wo, kh, kw, pad););
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_kx_gather_sum(const void* t, const float* bias, void* out, int N, int H, int Wt, int Wo, int kw, int co_real,
+                      int Ct, int Co, int dtype, void* stream) {
+  P2P_REQUIRE(t && out && N > 0 && H > 0 && kw > 0 && Wt == Wo + kw - 1, "bad geometry");
+  P2P_REQUIRE(co_real >= 1 && co_real <= 8 && kw * co_real <= Ct && Ct % 16 == 0 && Co % 16 == 0, "bad channel counts");
+  P2P_REQUIRE(H <= 65535 && N <= 65535, "map too large");
+  const int smem = dtype == P2P_BF16 ? (256 + kw - 1) * (Ct / 2 + 1) * 4 : 0;
+  P2P_REQUIRE(smem <= 48 * 1024, "fat map too wide for the staging buffer");
+  const dim3 grid((Wo + 255) / 256, H, N);
+  P2P_DISPATCH(dtype, kx_gather_sum_kernel<T><<<grid, 256, smem, as_stream(stream)>>>((const T*)t, bias, (T*)out, H, Wt, Wo,
+                                                                                     kw, co_real, Ct, Co););
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_kx_scatter(const void* dy, void* a, int N, int H, int Wo, int Wa, int kw, int co_real, int Cs, int Ca, int dtype,
+                   void* stream) {
+  P2P_REQUIRE(dy && a && N > 0 && H > 0 && kw > 0 && Wa == Wo + kw - 1, "bad geometry");
+  P2P_REQUIRE(co_real >= 1 && co_real <= Cs && kw * co_real <= Ca && Cs % 8 == 0 && Ca % 8 == 0, "bad channel counts");
+  const int64_t total = (int64_t)N * H * Wa * (Ca / 8);
+  P2P_DISPATCH(dtype, kx_scatter_kernel<T><<<ew_grid(total), 256, 0, as_stream(stream)>>>((const T*)dy, (T*)a, N, H, Wo, Wa,
+                                                                                         kw, co_real, Cs, Ca););
   P2P_LAUNCH_CHECK();
 }
 

@@ -154,6 +154,49 @@ class ConvPlan:
                            self.Co, self.Ci, self.k, self.k)
 
 
+class FatColumnConv:
+    """A stride-1 convolution with a wide filter and very few output channels (ExpandNetwork's last layer: 9x9,
+    32 -> 3) as a (k x 1) convolution with k*cout "fat" output channels plus a horizontal gather: one MMA column
+    per (kx, co) pair instead of 16 columns per filter tap.  Forward and data-gradient only (the weight gradient
+    keeps the layer's ordinary plan)."""
+
+    def __init__(self, N, Hi, Wi, Ci, cin_real, cout_real, k):
+        self.k, self.cin_real, self.cout_real, self.Ci = k, cin_real, cout_real, Ci
+        self.N, self.Hi, self.Wi = N, Hi, Wi
+        self.Ho, self.Wo = Hi - k + 1, Wi - k + 1
+        self.nfat = k * cout_real
+        self.Cf = pad16(self.nfat)
+        self.desc = Conv(N, Hi, Wi, Ci, self.Ho, Wi, self.Cf, k, 1, 1, 0, self.nfat, cin_real, L.ACT_NONE)
+        self.wp = self.wt = self.w2 = None
+
+    @staticmethod
+    def applies(cout_real, k, dt) -> bool:
+        return k >= 5 and cout_real <= 4 and dt == torch.bfloat16 and _state["impl"] == L.IMPL_AUTO
+
+    def pack_job(self, weight, dt) -> L.PackJob:
+        # W'[(kx*cout + co)][ci][ky][0] = w[co][ci][ky][kx]
+        self.w2 = weight.detach().permute(3, 0, 1, 2).reshape(self.nfat, self.cin_real, self.k, 1).contiguous()
+        dev = weight.device
+        self.wp = _empty((self.Cf, self.k, 1, self.Ci), dt, dev)
+        self.wt = _empty((self.Ci, self.k, 1, self.Cf), dt, dev)
+        return L.PackJob(ptr(self.w2), None, ptr(self.wp), ptr(self.wt), self.nfat, self.cin_real, self.Cf, self.Ci,
+                         self.k, 1)
+
+    def fwd(self, x, bias, out):
+        dc = L.dtype_code(x.dtype)
+        t = _empty((self.N, self.Ho, self.Wi, self.Cf), x.dtype, x.device)
+        call("p2p_conv_fwd", C.byref(self.desc), ptr(x), ptr(self.wp), None, ptr(t), None, dc, _state["impl"])
+        call("p2p_kx_gather_sum", ptr(t), ptr(bias), ptr(out), self.N, self.Ho, self.Wi, self.Wo, self.k, self.cout_real,
+             self.Cf, out.shape[3], dc)
+
+    def dgrad(self, dout, din):
+        dc = L.dtype_code(dout.dtype)
+        a = _empty((self.N, self.Ho, self.Wi, self.Cf), dout.dtype, dout.device)
+        call("p2p_kx_scatter", ptr(dout), ptr(a), self.N, self.Ho, self.Wo, self.Wi, self.k, self.cout_real,
+             dout.shape[3], self.Cf, dc)
+        call("p2p_conv_dgrad", C.byref(self.desc), ptr(a), ptr(self.wt), ptr(din), dc, _state["impl"])
+
+
 # =====================================================================================================
 # Generator
 # =====================================================================================================
@@ -178,10 +221,10 @@ G_N = len(G_LAYERS)  # 24 conv + BatchNorm stages
 class _Stage:
     """One conv + BatchNorm + activation stage (or the long-skip add) and the buffers backward needs."""
     __slots__ = ("li", "plan", "x_in", "r", "sb", "skip", "skip_pad", "skip_src", "r_src", "act", "up", "pad",
-                 "H", "W", "C", "c_real", "role")
+                 "H", "W", "C", "c_real", "role", "fat")
 
     def __init__(self):
-        self.skip = self.skip_src = self.r_src = self.plan = self.x_in = self.sb = None
+        self.skip = self.skip_src = self.r_src = self.plan = self.x_in = self.sb = self.fat = None
         self.skip_pad = 0
         self.li = -1
 
@@ -216,6 +259,12 @@ class GeneratorFunction(torch.autograd.Function):
             jobs.append(pk.pack_job(params[4 * len(packs)], None, dt))
             packs.append(pk)
             ci = cout
+        fat = None
+        _ln, _lbn, l_cout, l_k, _ls, _la, _lr = G_LAYERS[-1]
+        if FatColumnConv.applies(l_cout, l_k, dt):
+            # the last layer reads the H x W map padded by l_k // 2 (written by the stage before it)
+            fat = FatColumnConv(B, H + 2 * (l_k // 2), W + 2 * (l_k // 2), packs[-1].Ci, packs[-1].cin_real, l_cout, l_k)
+            jobs.append(fat.pack_job(params[4 * (G_N - 1)], dt))
         L.call_multi("p2p_pack_weights_multi", jobs, dc)
         stats_slab = _zeros((sum(2 * pk.Co for pk in packs),), torch.float64, dev) if training else None
         stats_off = 0
@@ -228,12 +277,18 @@ class GeneratorFunction(torch.autograd.Function):
             r = _empty((B, Ho, Wo, Co), dt, dev)
             stats = stats_slab[stats_off: stats_off + 2 * Co] if training else None
             stats_off += 2 * Co
-            plan.fwd(cur, b, r, stats)
+            if fat is not None and li == G_N - 1:
+                fat.fwd(cur, b, r)
+                if stats is not None:
+                    call("p2p_channel_stats", ptr(r), ptr(stats), B * Ho * Wo, Co, dc)
+            else:
+                plan.fwd(cur, b, r, stats)
             sb = _empty((4 * Co,), torch.float32, dev)
             call("p2p_bn_finalize", ptr(stats), B * Ho * Wo, ptr(gamma), ptr(beta), ptr(rm), ptr(rv), ptr(nbt), ptr(sb),
                  cout, Co, 1 if training else 0)
             st = _Stage()
             st.li, st.plan, st.x_in, st.r, st.sb, st.act, st.role = li, plan, cur, r, sb, act, role
+            st.fat = fat if li == G_N - 1 else None
             st.H, st.W, st.C, st.c_real = Ho, Wo, Co, cout
             if role == "res_a":
                 block_in, block_in_src = cur, producer
@@ -343,7 +398,7 @@ class GeneratorFunction(torch.autograd.Function):
                 st.x_in, dr, acc_slab[acc_off[id(st)]: acc_off[id(st)] + st.plan.acc_numel()], gw))
             if li > 0:
                 dpad = _empty(tuple(st.x_in.shape), dt, dev)
-                st.plan.dgrad(dr, dpad)
+                (st.fat or st.plan).dgrad(dr, dpad)
             else:
                 dpad = None
         L.call_multi("p2p_unpack_wgrad_multi", unpack_jobs)

@@ -365,3 +365,34 @@ def test_batched_pack_unpack_and_sigma_correction_match_single_calls(dt):
     call_multi("p2p_sn_weight_grad_multi", sn_jobs)
     for acc, g_multi, g_single, dot_m, dot_s, sigma, u, v, cout, cin, k in checks:
         assert relerr(g_multi, g_single) <= 1e-4
+
+
+@pytest.mark.parametrize("shape", [(2, 32, 3, 20, 28, 9), (1, 16, 2, 13, 300, 5)])
+def test_fat_column_conv_matches_conv2d(shape):
+    """(k x 1) convolution with k*cout fat channels + horizontal gather == the k x k convolution; its dgrad too."""
+    B, cin, cout, H, W, k = shape
+    dt = torch.bfloat16
+    g = torch.Generator(device="cpu").manual_seed(21)
+    x = torch.randn(B, cin, H + k - 1, W + k - 1, generator=g).to(DEV)
+    w = (torch.randn(cout, cin, k, k, generator=g) / math.sqrt(cin * k * k)).to(DEV)
+    bias = torch.randn(cout, generator=g).to(DEV)
+    Ci, Co = E.pad16(cin), E.pad16(cout)
+    xs = to_stored(x, Ci, dt)
+    assert E.FatColumnConv.applies(cout, k, dt)
+    fat = E.FatColumnConv(B, H + k - 1, W + k - 1, Ci, cin, cout, k)
+    L.call_multi("p2p_pack_weights_multi", [fat.pack_job(w, dt)], L.BF16)
+    out = torch.full((B, H, W, Co), 5.0, dtype=dt, device=DEV)
+    fat.fwd(xs, bias, out)
+    xr = from_stored(xs, cin).float().requires_grad_(True)
+    wr = w.to(dt).float()
+    ref = F.conv2d(xr, wr, bias)
+    assert relerr(from_stored(out, cout), ref) <= 1.5e-2          # one extra bf16 rounding of the per-kx partial sums
+    assert out[..., cout:].abs().max().item() == 0
+    go = torch.randn(ref.shape, generator=g).to(DEV)
+    gos = to_stored(go, Co, dt)
+    ref.backward(from_stored(gos, cout).float())
+    din = torch.full_like(xs, 5.0)
+    fat.dgrad(gos, din)
+    assert relerr(from_stored(din, cin), xr.grad) <= 1e-2
+    if Ci > cin:
+        assert din[..., cin:].abs().max().item() == 0
