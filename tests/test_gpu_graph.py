@@ -98,3 +98,25 @@ def test_adam_device_step_matches_host_step():
         call("p2p_adam_step_dev", ptr(p), ptr(grad), ptr(m), ptr(v), n, 2e-4, 0.5, 0.999, 1e-8, ptr(step_t), 0.5)
     for x, y in zip(*state):
         assert torch.allclose(x, y, rtol=1e-6, atol=1e-9)
+
+
+def test_prefetch_stages_the_next_batch():
+    """step() after prefetch() of the same pinned tensors == step() that copies them itself (fp32 mode)."""
+    import p2p_pytorch_b200 as P
+    P.set_precision("fp32")
+    batches = [tuple(t.pin_memory() for t in orc.synthetic_batch(2, 32, 32, 70 + i)) for i in range(5)]
+    losses = {}
+    for use_prefetch in (False, True):
+        g, d = _nets(P)
+        tr = P.Pix2PixTrainer(g, d, cuda_graph=True, graph_warmup=1)
+        rec = []
+        if use_prefetch:
+            tr.prefetch(*batches[0])
+        for i, bt in enumerate(batches):
+            out = tr.step(*bt)
+            if use_prefetch and i + 1 < len(batches):
+                tr.prefetch(*batches[i + 1])
+            rec.append((out["loss_d"].item(), out["loss_g"].item()))
+        losses[use_prefetch] = rec
+    for (d0, g0), (d1, g1) in zip(losses[False], losses[True]):
+        assert abs(d0 - d1) <= 1e-3 * abs(d0) and abs(g0 - g1) <= 1e-3 * abs(g0)
