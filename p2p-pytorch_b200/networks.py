@@ -243,12 +243,15 @@ class MultiscaleDiscriminator(nn.Module):
             params = [p.detach() for p in params]
         return params, refs, sn_bufs
 
-    def forward_stored(self, a, b=None, frozen=False):
+    def forward_stored(self, a, b=None, frozen=False, first_layer_cache=None):
         """15 stored maps (scale-major, full resolution first).  `frozen=True` treats the weights as constants:
         gradients still reach the input, no weight gradients are computed (what `loss_g.backward()` needs;
-        the reference computes and then discards them, train.py:385-388)."""
+        the reference computes and then discards them, train.py:385-388).
+        `first_layer_cache`: a dict shared by two passes over the SAME image pair between two optimizer steps (the
+        caller's promise): the first pass fills it, the second reuses the input pyramid and the outputs of the first
+        layer (no spectral norm there, so they are bit-identical) instead of recomputing them."""
         params, refs, sn_bufs = self._gather(frozen)
-        aux = dict(layer_cfg=self._cfg, sn_bufs=sn_bufs, param_refs=refs)
+        aux = dict(layer_cfg=self._cfg, sn_bufs=sn_bufs, param_refs=refs, first_layer_cache=first_layer_cache)
         outs = E.DiscriminatorFunction.apply(a, b, aux, *params)
         nl = len(self._cfg)
         return [list(outs[i * nl:(i + 1) * nl]) for i in range(self.num_D)]

@@ -166,12 +166,13 @@ class Pix2PixTrainer:
         last = lambda maps: [s[-1] for s in maps]                                         # noqa: E731
         ones = [1] * 3
         fake_b = net_g(g_input)                                                           # train.py:300
-        pred_fake_d = net_d.forward_stored(real_a, fake_b.detach())                       # :308-309
+        share = {}                                         # passes 1 and 3 see the same pair: pyramid + layer 0 once
+        pred_fake_d = net_d.forward_stored(real_a, fake_b.detach(), first_layer_cache=share)   # :308-309
         loss_d_fake = lsgan_loss(last(pred_fake_d), ones, 0.0)                            # :310
         pred_real = net_d.forward_stored(real_a, real_b)                                  # :315-316
         loss_d_real = lsgan_loss(last(pred_real), ones, 1.0)                              # :317
         loss_d = (loss_d_fake + loss_d_real) * 0.5                                        # :320
-        pred_fake = net_d.forward_stored(real_a, fake_b, frozen=True)                     # :336-337
+        pred_fake = net_d.forward_stored(real_a, fake_b, frozen=True, first_layer_cache=share)   # :336-337
         loss_g_gan = lsgan_loss(last(pred_fake), ones, 1.0)                               # :338
         loss_feat = feature_matching_loss(pred_fake, pred_real, cr)                       # :344-351
         loss_tv = tv_loss(fake_b)                                                         # :378
