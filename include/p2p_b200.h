@@ -217,6 +217,15 @@ int p2p_kx_gather_sum(const void* t, const float* bias, void* out, int N, int H,
                       int Ct, int Co, int dtype, void* stream);
 int p2p_kx_scatter(const void* dy, void* a, int N, int H, int Wo, int Wa, int kw, int co_real, int Cs, int Ca, int dtype,
                    void* stream);
+
+/* ---- compression front end: CompressionNetwork.forward (networks.py:201-236) ---------------
+ * Its three convolutions are p2p_conv_fwd calls (5x5 3->64, 3x3 64->64 with BatchNorm statistics, 3x3 stride 2
+ * 64->12) glued with p2p_nchw_to_nhwc / p2p_bn_act_store / p2p_bn_finalize; this is the tail:
+ * PixelShuffle(2) of res [B,H/2,W/2,16] (12 real channels), F.normalize over the 3 output channels, + x (NCHW fp32),
+ * written to y (net_c's output, may be NULL) and/or, quantised to 2^bits - 1 levels as compress() of
+ * generate_dataset.py:29-34 does for train.py:297, to `compressed` (may be NULL); both NCHW fp32 [B,3,H,W]. */
+int p2p_c_output(const void* res, const float* x, float* y, float* compressed, int B, int H, int W, int bits, int dtype,
+                 void* stream);
 /* stored map [B,H,W,C] dtype <-> NCHW fp32 [B,c_real,H,W] (drop-in API edge). */
 int p2p_nhwc_to_nchw(const void* in, float* out, int B, int H, int W, int C, int c_real, int dtype, void* stream);
 int p2p_nchw_to_nhwc(const float* in, void* out, int B, int H, int W, int C, int c_real, int dtype, void* stream);

@@ -16,3 +16,9 @@ def fingerprint(t: torch.Tensor) -> np.ndarray:
     head = torch.zeros(13, dtype=torch.float64)
     head[: min(13, f.numel())] = f[:13]
     return torch.cat([torch.stack([f.sum(), f.abs().sum(), (f * f).sum()]), head]).numpy()
+
+C_CASES = [  # compression front end: name, batch, H, W, data seed, train-mode BatchNorm
+    ("b2_32x32", 2, 32, 32, 123, True),
+    ("b1_64x48_eval", 1, 64, 48, 7, False),
+    ("b3_32x40", 3, 32, 40, 11, True),
+]

@@ -2,13 +2,14 @@
 sm_100a kernels, behind the reference's own `networks.py` API.  Import as `p2p_pytorch_b200`."""
 from . import _lib
 from .engine import get_precision, set_precision
-from .networks import (GANLoss, MultiscaleDiscriminator, ExpandNetwork, define_D, define_G, init_net, init_weights)
+from .networks import (CompressionNetwork, GANLoss, MultiscaleDiscriminator, ExpandNetwork, define_C, define_D, define_G,
+                       init_net, init_weights)
 from .losses import feature_matching_loss, lsgan_loss, tv_loss
 from .optim import FusedAdam
 from .trainer import Pix2PixTrainer
 
 _lib.load()   # fail at import time if the CUDA library has not been built: there is no fallback path
 
-__all__ = ["define_G", "define_D", "GANLoss", "init_net", "init_weights", "ExpandNetwork", "MultiscaleDiscriminator",
+__all__ = ["define_G", "define_D", "define_C", "CompressionNetwork", "GANLoss", "init_net", "init_weights", "ExpandNetwork", "MultiscaleDiscriminator",
            "FusedAdam", "Pix2PixTrainer", "lsgan_loss", "feature_matching_loss", "tv_loss", "set_precision",
            "get_precision"]

@@ -90,6 +90,7 @@ SIGNATURES = {
     "p2p_tap_scatter": [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp],
     "p2p_kx_gather_sum": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp],
     "p2p_kx_scatter": [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp],
+    "p2p_c_output": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp],
     "p2p_nhwc_to_nchw": [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp],
     "p2p_nchw_to_nhwc": [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp],
     "p2p_mse_const_fwd": [_vp, _f, _f, _vp, _i64, _i, _i, _i, _vp],

@@ -819,6 +819,39 @@ __global__ void __launch_bounds__(256) kx_scatter_kernel(const T* __restrict__ d
   }
 }
 
+// =================================================================================================
+// Tail of the compression front end (CompressionNetwork.forward, networks.py:226-236, + compress, train.py:297):
+// PixelShuffle(2) of the 12-channel map, L2-normalise over the 3 output channels, add the input image, and
+// optionally quantise to 2^bits - 1 levels (generate_dataset.py:29-34).  One thread per low-resolution pixel.
+// =================================================================================================
+template <typename T>
+__global__ void __launch_bounds__(256) c_output_kernel(const T* __restrict__ res, const float* __restrict__ x,
+                                                       float* __restrict__ y, float* __restrict__ comp, int B, int H,
+                                                       int W, float levels) {
+  const int h2 = H >> 1, w2 = W >> 1;
+  const int64_t total = (int64_t)B * h2 * w2;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int j = (int)(i % w2), ii = (int)((i / w2) % h2), n = (int)(i / ((int64_t)w2 * h2));
+    float v[16];
+    ld8(res + (size_t)i * 16, v);
+    ld8(res + (size_t)i * 16 + 8, v + 8);
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {                     // sub-pixel (dy, dx) = (s >> 1, s & 1); channel c reads 4c + s
+      const float a = v[s], b = v[4 + s], c = v[8 + s];
+      const float inv = 1.f / fmaxf(sqrtf(a * a + b * b + c * c), 1e-12f);      // F.normalize(p=2, dim=1, eps=1e-12)
+      const int yy = 2 * ii + (s >> 1), xx = 2 * j + (s & 1);
+      const float r3[3] = {a * inv, b * inv, c * inv};
+#pragma unroll
+      for (int ch = 0; ch < 3; ++ch) {
+        const size_t o = (((size_t)n * 3 + ch) * H + yy) * W + xx;
+        const float out = x[o] + r3[ch];
+        if (y != nullptr) y[o] = out;
+        if (comp != nullptr) comp[o] = rintf(fminf(fmaxf(out, 0.f), 1.f) * levels) / levels;
+      }
+    }
+  }
+}
+
 }  // namespace p2p
 
 using namespace p2p;
@@ -1023,6 +1056,16 @@ int p2p_kx_scatter(const void* dy, void* a, int N, int H, int Wo, int Wa, int kw
   const int64_t total = (int64_t)N * H * Wa * (Ca / 8);
   P2P_DISPATCH(dtype, kx_scatter_kernel<T><<<ew_grid(total), 256, 0, as_stream(stream)>>>((const T*)dy, (T*)a, N, H, Wo, Wa,
                                                                                          kw, co_real, Cs, Ca););
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_c_output(const void* res, const float* x, float* y, float* compressed, int B, int H, int W, int bits, int dtype,
+                 void* stream) {
+  P2P_REQUIRE(res && x && (y || compressed), "null pointer");
+  P2P_REQUIRE(B > 0 && H > 0 && W > 0 && H % 2 == 0 && W % 2 == 0 && bits >= 1 && bits <= 16, "bad geometry");
+  const int64_t total = (int64_t)B * (H / 2) * (W / 2);
+  P2P_DISPATCH(dtype, c_output_kernel<T><<<ew_grid(total), 256, 0, as_stream(stream)>>>(
+                          (const T*)res, x, y, compressed, B, H, W, (float)((1 << bits) - 1)););
   P2P_LAUNCH_CHECK();
 }
 

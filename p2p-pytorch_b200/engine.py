@@ -644,3 +644,58 @@ class StoredToNCHW(torch.autograd.Function):
         out = _empty((B, H, W, Cs), dt, g.device)
         call("p2p_nchw_to_nhwc", ptr(g), ptr(out), B, H, W, Cs, c_real, L.dtype_code(dt))
         return out, None
+
+
+# =====================================================================================================
+# Compression front end: CompressionNetwork.forward, reference networks.py:201-236
+# =====================================================================================================
+@torch.no_grad()
+def compression_forward(x, convs, prelus, bn, training: bool, bits: Optional[int] = None, want_y: bool = True):
+    """net_c(x) and/or compress(net_c(x), bits), forward only (the G/D iteration consumes it detached, train.py:300).
+    convs = [(weight, bias)] x 3 (5x5 3->64, 3x3 64->64, 3x3 stride 2 64->12); prelus = the two PReLU scalars;
+    bn = (gamma, beta, running_mean, running_var, num_batches_tracked) of the one BatchNorm.
+    Returns (y or None, compressed or None), NCHW fp32."""
+    L.require_cuda(x, "compression network input")
+    if x.dim() != 4 or x.shape[1] != 3 or x.shape[2] % 2 or x.shape[3] % 2:
+        raise L.P2PError("compression network input must be [B,3,H,W] with even H, W")
+    B, _, H, W = x.shape
+    dt, dev = _state["dtype"], x.device
+    dc = L.dtype_code(dt)
+    x = x.detach().contiguous().float()
+    geo = [(3, 64, 5, 1), (64, 64, 3, 1), (64, 12, 3, 2)]
+    plans, jobs = [], []
+    hin, win = H, W
+    for (cin, cout, k, stride), (w, _b) in zip(geo, convs):
+        pl = ConvPlan(B, hin + 2 * (k // 2), win + 2 * (k // 2), pad16(cin), cin, cout, k, stride, 0)
+        jobs.append(pl.pack_job(w, None, dt, want_wt=False))
+        plans.append(pl)
+        hin, win = pl.Ho, pl.Wo
+    L.call_multi("p2p_pack_weights_multi", jobs, dc)
+    # input: NCHW fp32 -> NHWC (16 stored channels) -> reflection pad 2
+    x_nhwc = _empty((B, H, W, 16), dt, dev)
+    call("p2p_nchw_to_nhwc", ptr(x), ptr(x_nhwc), B, H, W, 16, 3, dc)
+    cur = _empty((B, H + 4, W + 4, 16), dt, dev)
+    call("p2p_bn_act_store", ptr(x_nhwc), None, None, 0, None, ptr(cur), None, B, H, W, 16, 3, L.ACT_NONE, 1, 2, dc)
+    # conv_input: 5x5 conv + PReLU, stored with the reflection pad 1 of the next conv
+    r = _empty((B, H, W, 64), dt, dev)
+    plans[0].fwd(cur, convs[0][1], r, None)
+    cur = _empty((B, H + 2, W + 2, 64), dt, dev)
+    call("p2p_bn_act_store", ptr(r), None, None, 0, ptr(prelus[0]), ptr(cur), None, B, H, W, 64, 64, L.ACT_PRELU, 1, 1, dc)
+    # conv_block1: 3x3 conv + BatchNorm + PReLU
+    gamma, beta, rm, rv, nbt = bn
+    r = _empty((B, H, W, 64), dt, dev)
+    stats = _zeros((128,), torch.float64, dev) if training else None
+    plans[1].fwd(cur, convs[1][1], r, stats)
+    sb = _empty((256,), torch.float32, dev)
+    call("p2p_bn_finalize", ptr(stats), B * H * W, ptr(gamma), ptr(beta), ptr(rm), ptr(rv), ptr(nbt), ptr(sb), 64, 64,
+         1 if training else 0)
+    cur = _empty((B, H + 2, W + 2, 64), dt, dev)
+    call("p2p_bn_act_store", ptr(r), ptr(sb), None, 0, ptr(prelus[1]), ptr(cur), None, B, H, W, 64, 64, L.ACT_PRELU, 1, 1,
+         dc)
+    # conv_block2: 3x3 stride-2 conv to 12 channels; PixelShuffle + normalize + identity (+ compress) in one kernel
+    res = _empty((B, H // 2, W // 2, 16), dt, dev)
+    plans[2].fwd(cur, convs[2][1], res, None)
+    y = _empty((B, 3, H, W), torch.float32, dev) if want_y else None
+    comp = _empty((B, 3, H, W), torch.float32, dev) if bits is not None else None
+    call("p2p_c_output", ptr(res), ptr(x), ptr(y), ptr(comp), B, H, W, bits if bits is not None else 3, dc)
+    return y, comp

@@ -65,6 +65,11 @@ def define_G(init_type="normal", init_gain=0.02, gpu_id="cuda:0"):
     return init_net(ExpandNetwork(), init_type, init_gain, gpu_id)
 
 
+def define_C(init_type="normal", init_gain=0.02, gpu_id="cuda:0"):
+    """reference networks.py:157-162"""
+    return init_net(CompressionNetwork(), init_type, init_gain, gpu_id)
+
+
 def define_D(input_nc, ndf, norm="batch", use_sigmoid=False, init_type="normal", init_gain=0.02, gpu_id="cuda:0"):
     # `norm` is accepted and ignored, as in the reference (networks.py:712 passes norm_layer=None)
     net = MultiscaleDiscriminator(input_nc, ndf, n_layers=3, norm_layer=None, use_sigmoid=use_sigmoid, num_D=3,
@@ -265,6 +270,38 @@ class MultiscaleDiscriminator(nn.Module):
                 row.append(E.StoredToNCHW.apply(t, self._cfg[j][1]))
             result.append(row)
         return result
+
+
+# -----------------------------------------------------------------------------------------------------
+# compression front end (reference networks.py:201-236)
+# -----------------------------------------------------------------------------------------------------
+class CompressionNetwork(nn.Module):
+    """The network `define_C` returns: same sub-module structure and state_dict keys as the reference.  FORWARD
+    ONLY: the G/D iteration consumes `compress(net_c(real_b), 3).detach()` (train.py:297-300); training net_c
+    itself is phase 3 of the reference loop (train.py:392-402), which is out of scope, so the output carries no
+    grad_fn."""
+
+    def __init__(self):
+        super().__init__()
+        self.conv_input = nn.Sequential(ConvLayer(3, 64, kernel_size=5, stride=1), nn.PReLU())
+        self.conv_block1 = nn.Sequential(ConvLayer(64, 64, kernel_size=3, stride=1), nn.BatchNorm2d(64), nn.PReLU())
+        self.conv_block2 = nn.Sequential(ConvLayer(64, 12, kernel_size=3, stride=2), nn.PixelShuffle(2))
+
+    def _run(self, x, bits, want_y):
+        c0, c1, c2 = self.conv_input[0].conv2d, self.conv_block1[0].conv2d, self.conv_block2[0].conv2d
+        bn = self.conv_block1[1]
+        return E.compression_forward(
+            x, [(c0.weight, c0.bias), (c1.weight, c1.bias), (c2.weight, c2.bias)],
+            [self.conv_input[1].weight, self.conv_block1[2].weight],
+            (bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.num_batches_tracked), self.training, bits, want_y)
+
+    def forward(self, x):
+        """identity + normalize(pixel_shuffle(convs(x))) -- networks.py:222-236"""
+        return self._run(x, None, True)[0]
+
+    def front_end(self, real_b, bits=3):
+        """compress(net_c(real_b), bits): the generator's input (train.py:297, :466) in one pass"""
+        return self._run(real_b, bits, False)[1]
 
 
 # -----------------------------------------------------------------------------------------------------

@@ -275,3 +275,54 @@ def test_loss_curves_track_oracle_200_steps():
     assert sum(close) >= len(close) - 2, close
     m, r = mine.mean(0), ref.mean(0)
     assert np.all(np.abs(m - r) <= 0.4 * np.abs(r)), (m, r)      # two oracle runs differ by up to ~0.3 here
+
+
+# ---- compression front end -----------------------------------------------------------------------
+from oracle.make_golden_util import C_CASES  # noqa: E402
+
+
+@pytest.mark.parametrize("case", C_CASES, ids=[c[0] for c in C_CASES])
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_compression_front_end_matches_reference_golden(case, precision):
+    """define_C's forward and compress(net_c(real_b), 3) against the vectors from the unmodified reference."""
+    import p2p_pytorch_b200 as P
+    name, batch, h, w, seed, training = case
+    gold = np.load(os.path.join(GOLD, f"ref_netc_{name}.npz"))
+    P.set_precision(precision)
+    net = P.CompressionNetwork().to(DEV)
+    net.load_state_dict(orc.init_c_state(125))
+    net.train(training)
+    _a, real_b, _c = orc.synthetic_batch(batch, h, w, seed)
+    y = net(real_b.to(DEV)).cpu().numpy()
+    sd = {k: v.cpu() for k, v in net.state_dict().items()}
+    net2 = P.CompressionNetwork().to(DEV)
+    net2.load_state_dict(orc.init_c_state(125))
+    net2.train(training)
+    comp = net2.front_end(real_b.to(DEV)).cpu().numpy()
+    # fp32 mode: exact arithmetic; bf16 mode: the residual is a unit vector per pixel, bf16 convs move it by < 2e-2
+    tol = 2e-5 if precision == "fp32" else 3e-2
+    assert np.abs(y - gold["y"]).max() <= tol
+    # quantised output: levels may flip only where the reference value sits within `tol` of a rounding boundary
+    frac = gold["y"].clip(0, 1) * 7
+    near = np.abs(frac - np.floor(frac) - 0.5) <= tol * 7 + 1e-6
+    diff = np.abs(comp - gold["compressed"])
+    assert diff.max() <= 1.0 / 7 + 1e-6 and not np.any((diff > 1e-6) & ~near)
+    assert set(np.unique(np.round(comp * 7)).tolist()) <= set(range(8))
+    if training:
+        rtol = 1e-4 if precision == "fp32" else 2e-2
+        assert np.allclose(sd["conv_block1.1.running_mean"].numpy(), gold["running_mean"], rtol=rtol, atol=rtol * 1e-1)
+        assert np.allclose(sd["conv_block1.1.running_var"].numpy(), gold["running_var"], rtol=rtol, atol=rtol * 1e-1)
+        assert int(sd["conv_block1.1.num_batches_tracked"]) == 1
+    else:
+        assert int(sd["conv_block1.1.num_batches_tracked"]) == 0
+
+
+def test_define_c_is_a_drop_in():
+    import p2p_pytorch_b200 as P
+    net = P.define_C("normal", 0.02, gpu_id=DEV)
+    assert list(net.state_dict().keys()) == list(orc.init_c_state(125).keys())
+    assert sum(p.numel() for p in net.parameters()) == sum(v.numel() for k, v in orc.init_c_state(125).items()
+                                                           if "running" not in k and "num_batches" not in k)
+    x = torch.rand(2, 3, 64, 64, device=DEV) * 2 - 1
+    out = net.front_end(x)
+    assert out.shape == x.shape and out.dtype == torch.float32 and not out.requires_grad

@@ -128,3 +128,24 @@ def test_state_dict_keys_match_reference_inventory():
     assert list(g)[0] == "relu.weight" and list(g)[-1] == "in1_d.num_batches_tracked"
     assert list(d)[2:6] == ["scale0_layer1.0.module.bias", "scale0_layer1.0.module.weight_u",
                             "scale0_layer1.0.module.weight_v", "scale0_layer1.0.module.weight_bar"]
+
+
+@pytest.mark.parametrize("case", __import__("oracle.make_golden_util", fromlist=["C_CASES"]).C_CASES,
+                         ids=[c[0] for c in __import__("oracle.make_golden_util", fromlist=["C_CASES"]).C_CASES])
+def test_oracle_front_end_matches_reference_golden(case):
+    """CompressionNetwork.forward + compress(., 3) against vectors from the unmodified reference
+    (oracle/make_golden_c.py)."""
+    name, batch, h, w, seed, training = case
+    gold = np.load(os.path.join(GOLD, f"ref_netc_{name}.npz"))
+    s = orc.init_c_state(125)
+    _a, real_b, _c = orc.synthetic_batch(batch, h, w, seed)
+    with torch.no_grad():
+        y = orc.c_forward(s, real_b, training)
+        comp = orc.compress(y, 3)
+    assert np.abs(y.numpy() - gold["y"]).max() <= 1e-5
+    # 3-bit quantisation: a value within 1e-5 of a rounding boundary may land on the neighbouring level
+    flips = np.abs(comp.numpy() - gold["compressed"]) > 1e-6
+    assert flips.mean() <= 1e-3 and np.abs(comp.numpy() - gold["compressed"]).max() <= 1.0 / 7 + 1e-6
+    assert np.abs(s["conv_block1.1.running_mean"].numpy() - gold["running_mean"]).max() <= 1e-6
+    assert np.abs(s["conv_block1.1.running_var"].numpy() - gold["running_var"]).max() <= 1e-6
+    assert int(s["conv_block1.1.num_batches_tracked"]) == int(gold["num_batches_tracked"])
