@@ -240,6 +240,10 @@ int p2p_mse_const_bwd(const void* p, float target, float weight, const float* gs
                       int c_real, int dtype, void* stream);
 /* the same on a flat fp32 array of n elements (GANLoss applied to tensors this library did not produce). */
 int p2p_mse_flat_fwd(const float* p, float target, float weight, float* loss, int64_t n, void* stream);
+/* *loss += weight * mean((a - b)^2) over two flat fp32 arrays: nn.MSELoss(reduction='mean') of train.py:30, used
+ * for phase 3's loss_c (train.py:394).  Forward value only: its gradient reaches net_c through torch.round, i.e.
+ * it is identically zero (quirk Q3). */
+int p2p_mse_pair_fwd(const float* a, const float* b, float weight, float* loss, int64_t n, void* stream);
 int p2p_mse_flat_bwd(const float* p, float target, float weight, const float* gscale, float* g, int64_t n,
                      void* stream);
 /* *loss += weight * mean|f - r| ; g = gscale * weight * sign(f - r) / n. */

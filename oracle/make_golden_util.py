@@ -22,3 +22,8 @@ C_CASES = [  # compression front end: name, batch, H, W, data seed, train-mode B
     ("b1_64x48_eval", 1, 64, 48, 7, False),
     ("b3_32x40", 3, 32, 40, 11, True),
 ]
+
+P3_CASES = [  # whole iteration with front end and phase 3: name, batch, H, W, steps, data seed
+    ("b2_32x32", 2, 32, 32, 2, 123),
+    ("b1_64x48", 1, 64, 48, 1, 7),
+]

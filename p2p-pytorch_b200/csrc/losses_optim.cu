@@ -76,6 +76,18 @@ __global__ void mse_flat_bwd_kernel(const float* __restrict__ p, float target, f
     g[i] = (p[i] - target) * s;
 }
 
+// ---- mean squared error between two flat fp32 arrays (phase 3's loss_c, train.py:394; forward value only) ----
+__global__ void __launch_bounds__(256) mse_pair_fwd_kernel(const float* __restrict__ a, const float* __restrict__ b,
+                                                           float coef, float* __restrict__ loss, int64_t n) {
+  float acc = 0.f;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float d = a[i] - b[i];
+    acc = fmaf(d, d, acc);
+  }
+  const float tot = block_sum<float>(acc);
+  if (threadIdx.x == 0) atomicAdd(loss, tot * coef);
+}
+
 // ---- total variation on NCHW fp32 -------------------------------------------------------------------
 __global__ void __launch_bounds__(256) tv_fwd_kernel(const float* __restrict__ x, float* __restrict__ loss, int64_t planes,
                                                      int H, int W, float cw, float ch) {
@@ -189,6 +201,12 @@ int p2p_mse_const_bwd(const void* p, float target, float weight, const float* gs
 int p2p_mse_flat_fwd(const float* p, float target, float weight, float* loss, int64_t n, void* stream) {
   P2P_REQUIRE(p && loss && n > 0, "bad arguments");
   mse_flat_fwd_kernel<<<red_grid(n), 256, 0, as_stream(stream)>>>(p, target, weight / (float)n, loss, n);
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_mse_pair_fwd(const float* a, const float* b, float weight, float* loss, int64_t n, void* stream) {
+  P2P_REQUIRE(a && b && loss && n > 0, "bad arguments");
+  mse_pair_fwd_kernel<<<red_grid(n), 256, 0, as_stream(stream)>>>(a, b, weight / (float)n, loss, n);
   P2P_LAUNCH_CHECK();
 }
 

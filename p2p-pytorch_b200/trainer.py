@@ -54,8 +54,8 @@ class Pix2PixTrainer:
     """optimizer_g / optimizer_d loop of train.py:241-242, :294-390."""
 
     def __init__(self, net_g, net_d, lr: float = 2e-4, beta1: float = 0.5, process_group=None,
-                 bucket_bytes: int = 64 << 20, cuda_graph: bool = False, graph_warmup: int = 2):
-        self.net_g, self.net_d = net_g, net_d
+                 bucket_bytes: int = 64 << 20, cuda_graph: bool = False, graph_warmup: int = 2, net_c=None):
+        self.net_g, self.net_d, self.net_c = net_g, net_d, net_c
         # cuda_graph=True: the first `graph_warmup` calls of step() run eagerly, the next one records the whole
         # iteration (~650 launches, both backward passes, the all-reduces and both Adam updates) into one CUDA
         # graph per input shape, and every later call is three input copies and one graph launch.  The host
@@ -122,6 +122,33 @@ class Pix2PixTrainer:
             pre["free"].record(torch.cuda.current_stream())         # the staging slot may be overwritten from here on
         rec["graph"].replay()
         return rec["outputs"]
+
+    def step_full(self, real_a: torch.Tensor, real_b: torch.Tensor, phase3: bool = True) -> Dict[str, torch.Tensor]:
+        """The iteration as the reference executes it (train.py:294-402, VGG terms off): the generator input is
+        compress(net_c(real_b), 3) (:297), then the G/D phases of step(), then phase 3 (:392-402).
+
+        Phase 3 in the reference is a second train-mode forward of net_g (with the weights optimizer_g has just
+        updated) on `compressed`, loss_c = MSE(., real_b), backward and optimizer_c.step().  Every gradient path
+        from loss_c to net_c runs through torch.round inside compress(), whose gradient is zero, so net_c receives
+        exact zeros and Adam leaves it unchanged (quirk Q3; pinned by tests/golden/ref_full_*.npz), and the
+        gradients it leaves in net_g are discarded by the next optimizer_g.zero_grad().  What persists -- and what
+        is done here, without the backward pass -- is the second update of every BatchNorm running buffer of G
+        (num_batches_tracked advances by 2 per iteration) and the value of loss_c."""
+        if self.net_c is None:
+            raise ValueError("step_full needs the compression network: Pix2PixTrainer(..., net_c=define_C(...))")
+        from . import _lib as L
+        real_b_dev = real_b.cuda(non_blocking=True) if not real_b.is_cuda else real_b
+        compressed = self.net_c.front_end(real_b_dev, 3)                                  # :297 (train-mode BatchNorm)
+        out = dict(self.step(real_a, real_b_dev, compressed))                             # :300-390
+        out["compressed"] = compressed
+        if phase3:
+            with torch.no_grad():
+                fake_after = self.net_g(compressed)                                       # :392
+                loss_c = torch.zeros((), dtype=torch.float32, device=compressed.device)
+                L.call("p2p_mse_pair_fwd", L.ptr(fake_after), L.ptr(real_b_dev.contiguous().float()), 1.0,
+                       L.ptr(loss_c), fake_after.numel())                                 # :394
+            out["loss_c"] = loss_c
+        return out
 
     def prefetch(self, real_a: torch.Tensor, real_b: torch.Tensor, g_input: torch.Tensor) -> None:
         """Start copying the NEXT batch (pinned host tensors) to the device on a side stream while the current

@@ -335,3 +335,38 @@ def test_define_c_is_a_drop_in():
     x = torch.rand(2, 3, 64, 64, device=DEV) * 2 - 1
     out = net.front_end(x)
     assert out.shape == x.shape and out.dtype == torch.float32 and not out.requires_grad
+
+
+# ---- the iteration as executed, with front end and phase 3 ------------------------------------------
+from oracle.make_golden_util import P3_CASES, fingerprint as _fp  # noqa: E402
+
+
+@pytest.mark.parametrize("case", P3_CASES, ids=[c[0] for c in P3_CASES])
+def test_full_iteration_with_phase3_matches_reference_golden(case):
+    """fp32 mode against vectors from the unmodified reference modules (oracle/make_golden_p3.py)."""
+    import p2p_pytorch_b200 as P
+    name, batch, h, w, steps, seed = case
+    gold = np.load(os.path.join(GOLD, f"ref_full_{name}.npz"))
+    P, g, d = build("fp32")
+    c = P.CompressionNetwork().to(DEV)
+    c.load_state_dict(orc.init_c_state(125))
+    c.train()
+    c0 = {k: v.detach().clone() for k, v in c.named_parameters()}
+    tr = P.Pix2PixTrainer(g, d, net_c=c)
+    for it in range(steps):
+        a, b, _ = orc.synthetic_batch(batch, h, w, seed + it)
+        out = tr.step_full(a.to(DEV), b.to(DEV))
+        p = f"s{it}."
+        scale = 25.0 if it else 1.0
+        for k in ("loss_d", "loss_g_gan", "loss_feat", "loss_tv", "loss_g", "loss_c"):
+            assert abs(out[k].item() - float(gold[p + k])) <= 2e-4 * scale * abs(float(gold[p + k])) + 1e-6, (it, k)
+        fp_c = _fp(out["compressed"].cpu())[:3]
+        assert np.allclose(fp_c, gold[p + "compressed"][:3], rtol=2e-3, atol=0.5)   # a few 1/7 level flips at most
+        assert np.allclose(_fp(out["fake_b"].cpu())[:3], gold[p + "fake_b"][:3], rtol=5e-3 * scale, atol=1e-2)
+        sd = {**{k: v for k, v in g.state_dict().items()}, **{"net_c." + k: v for k, v in c.state_dict().items()}}
+        for k, v in sd.items():
+            if "running" in k or "num_batches" in k:
+                assert np.allclose(_fp(v.double().cpu())[:3], gold[p + "buf." + k][:3], rtol=5e-3 * scale, atol=2e-3), (it, k)
+    assert all(torch.equal(c0[k], v.detach()) for k, v in c.named_parameters())     # quirk Q3: net_c never moves
+    assert int(g.state_dict()["in1_e.num_batches_tracked"]) == 2 * steps
+    assert int(c.state_dict()["conv_block1.1.num_batches_tracked"]) == steps

@@ -149,3 +149,35 @@ def test_oracle_front_end_matches_reference_golden(case):
     assert np.abs(s["conv_block1.1.running_mean"].numpy() - gold["running_mean"]).max() <= 1e-6
     assert np.abs(s["conv_block1.1.running_var"].numpy() - gold["running_var"]).max() <= 1e-6
     assert int(s["conv_block1.1.num_batches_tracked"]) == int(gold["num_batches_tracked"])
+
+
+_P3 = __import__("oracle.make_golden_util", fromlist=["P3_CASES"]).P3_CASES
+
+
+@pytest.mark.parametrize("case", _P3, ids=[c[0] for c in _P3])
+def test_oracle_full_iteration_with_phase3_matches_reference_golden(case):
+    """front end + G/D phases + phase 3 (train.py:294-402, VGG off) against vectors from the
+    unmodified reference modules (oracle/make_golden_p3.py), including quirk Q3: net_c never moves."""
+    name, batch, h, w, steps, seed = case
+    gold = np.load(os.path.join(GOLD, f"ref_full_{name}.npz"))
+    assert int(gold["c_params_moved"]) == 0
+    ot = orc.OracleFullTrainer(orc.init_g_state(123), orc.init_d_state(124), orc.init_c_state(125))
+    c0 = {k: ot.c[k].detach().clone() for k in ot.c_trainable}
+    for it in range(steps):
+        a, b, _ = orc.synthetic_batch(batch, h, w, seed + it)
+        out = ot.step_full(a, b)
+        p = f"s{it}."
+        scale = 25.0 if it else 1.0                      # Adam turns rounding noise into +-lr steps after step 0
+        for k in ("loss_d", "loss_g_gan", "loss_feat", "loss_tv", "loss_g", "loss_c"):
+            _close(out[k].item(), gold[p + k], 2e-5 * scale, 1e-6, p + k)
+        _close(fingerprint(out["compressed"])[:3], gold[p + "compressed"][:3], 1e-6, 1e-6, p + "compressed")
+        _close(fingerprint(out["fake_b"])[:3], gold[p + "fake_b"][:3], 2e-4 * scale, 1e-3, p + "fake_b")
+        assert float(gold[p + "c_grad_max"]) == 0.0
+        assert max(ot.c[k].grad.abs().max().item() for k in ot.c_trainable) == 0.0
+        for k, v in list(ot.g.items()) + [("net_c." + k, v) for k, v in ot.c.items()]:
+            if "running" in k or "num_batches" in k:
+                # the second forward runs on weights Adam has just moved; the conv biases in front of BatchNorm move
+                # by +-lr with the sign of float noise (see test above), which shifts running_mean by up to 0.1 * lr each
+                _close(fingerprint(v.double())[:3], gold[p + "buf." + k][:3], 2e-4 * scale, 1e-3, p + k)
+    assert all(torch.equal(c0[k], ot.c[k].detach()) for k in ot.c_trainable)
+    assert int(ot.g["in1_e.num_batches_tracked"]) == 2 * steps
