@@ -244,6 +244,10 @@ int p2p_mse_flat_fwd(const float* p, float target, float weight, float* loss, in
  * for phase 3's loss_c (train.py:394).  Forward value only: its gradient reaches net_c through torch.round, i.e.
  * it is identically zero (quirk Q3). */
 int p2p_mse_pair_fwd(const float* a, const float* b, float weight, float* loss, int64_t n, void* stream);
+/* Evaluation metric of the reference (psnr / tensor2img, train.py:32-42, :60-65): sse[n] += sum over image n of
+ * (u8(a) - u8(b))^2 with u8(x) = (uint8) clip(x * 255, 0, 255) (float32 multiply, truncation) -- exact integer
+ * sums; PSNR = 10 log10(255^2 * per_image / sse).  a, b: [B, per_image] fp32; sse: B zero-initialised uint64. */
+int p2p_psnr_sse(const float* a, const float* b, unsigned long long* sse, int B, int64_t per_image, void* stream);
 int p2p_mse_flat_bwd(const float* p, float target, float weight, const float* gscale, float* g, int64_t n,
                      void* stream);
 /* *loss += weight * mean|f - r| ; g = gscale * weight * sign(f - r) / n. */

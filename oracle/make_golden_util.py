@@ -27,3 +27,24 @@ P3_CASES = [  # whole iteration with front end and phase 3: name, batch, H, W, s
     ("b2_32x32", 2, 32, 32, 2, 123),
     ("b1_64x48", 1, 64, 48, 1, 7),
 ]
+
+PSNR_CASES = [  # name, H, W, seed, kind
+    ("noise_32x32", 32, 32, 1, "noise"), ("close_64x48", 64, 48, 2, "close"), ("out_of_range_40x40", 40, 40, 3, "wide"),
+    ("identical_16x16", 16, 16, 4, "same"),
+]
+
+
+def psnr_inputs(h, w, seed, kind):
+    """two images [1,3,H,W]; 'wide' leaves [0,1] so that the clip matters, 'same' gives mse = 0 (PSNR = inf)"""
+    g = torch.Generator().manual_seed(seed)
+    a = torch.rand(1, 3, h, w, generator=g)
+    if kind == "noise":
+        b = torch.rand(1, 3, h, w, generator=g)
+    elif kind == "close":
+        b = a + 0.02 * torch.randn(1, 3, h, w, generator=g)
+    elif kind == "wide":
+        a = a * 1.6 - 0.3
+        b = a + 0.1 * torch.randn(1, 3, h, w, generator=g)
+    else:
+        b = a.clone()
+    return a, b

@@ -97,6 +97,7 @@ SIGNATURES = {
     "p2p_mse_const_bwd": [_vp, _f, _f, _vp, _vp, _i64, _i, _i, _i, _vp],
     "p2p_mse_flat_fwd": [_vp, _f, _f, _vp, _i64, _vp],
     "p2p_mse_pair_fwd": [_vp, _vp, _f, _vp, _i64, _vp],
+    "p2p_psnr_sse": [_vp, _vp, _vp, _i, _i64, _vp],
     "p2p_mse_flat_bwd": [_vp, _f, _f, _vp, _vp, _i64, _vp],
     "p2p_l1_fwd": [_vp, _vp, _f, _vp, _i64, _i, _i, _i, _vp],
     "p2p_l1_bwd": [_vp, _vp, _f, _vp, _vp, _i64, _i, _i, _i, _vp],

@@ -111,6 +111,11 @@ __device__ __forceinline__ double warp_sum(double v) {
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
 }
+__device__ __forceinline__ unsigned long long warp_sum(unsigned long long v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
 // sum over the whole block (blockDim.x multiple of 32, <= 1024); result valid in thread 0
 template <typename F>
 __device__ __forceinline__ F block_sum(F v) {

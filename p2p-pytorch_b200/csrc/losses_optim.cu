@@ -88,6 +88,22 @@ __global__ void __launch_bounds__(256) mse_pair_fwd_kernel(const float* __restri
   if (threadIdx.x == 0) atomicAdd(loss, tot * coef);
 }
 
+// ---- evaluation metric (train.py:32-42, :60-65): sum of squared differences of the two images as uint8 --------
+// u8(x) = (uint8) clip(x * 255, 0, 255) -- float32 multiply, truncation -- so the sum is exact integer work
+__global__ void __launch_bounds__(256) psnr_sse_kernel(const float* __restrict__ a, const float* __restrict__ b,
+                                                       unsigned long long* __restrict__ sse, int64_t per_image) {
+  const float* pa = a + (size_t)blockIdx.y * per_image;
+  const float* pb = b + (size_t)blockIdx.y * per_image;
+  unsigned long long acc = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < per_image; i += (int64_t)gridDim.x * blockDim.x) {
+    const int qa = (int)fminf(fmaxf(pa[i] * 255.f, 0.f), 255.f), qb = (int)fminf(fmaxf(pb[i] * 255.f, 0.f), 255.f);
+    const int d = qa - qb;
+    acc += (unsigned long long)(d * d);
+  }
+  const unsigned long long tot = block_sum<unsigned long long>(acc);
+  if (threadIdx.x == 0 && tot != 0) atomicAdd(sse + blockIdx.y, tot);
+}
+
 // ---- total variation on NCHW fp32 -------------------------------------------------------------------
 __global__ void __launch_bounds__(256) tv_fwd_kernel(const float* __restrict__ x, float* __restrict__ loss, int64_t planes,
                                                      int H, int W, float cw, float ch) {
@@ -207,6 +223,14 @@ int p2p_mse_flat_fwd(const float* p, float target, float weight, float* loss, in
 int p2p_mse_pair_fwd(const float* a, const float* b, float weight, float* loss, int64_t n, void* stream) {
   P2P_REQUIRE(a && b && loss && n > 0, "bad arguments");
   mse_pair_fwd_kernel<<<red_grid(n), 256, 0, as_stream(stream)>>>(a, b, weight / (float)n, loss, n);
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_psnr_sse(const float* a, const float* b, unsigned long long* sse, int B, int64_t per_image, void* stream) {
+  P2P_REQUIRE(a && b && sse && B > 0 && B <= 65535 && per_image > 0, "bad arguments");
+  int64_t gx = (per_image + 255) / 256;
+  if (gx > 64) gx = 64;
+  psnr_sse_kernel<<<dim3((int)gx, B), 256, 0, as_stream(stream)>>>(a, b, sse, per_image);
   P2P_LAUNCH_CHECK();
 }
 

@@ -1,0 +1,60 @@
+"""Evaluation metric and checkpoint format of the reference.
+
+psnr(): train.py:60-65 on the device -- the images are quantised to uint8 exactly as tensor2img does
+(train.py:32-42: x * 255 in float32, clip, truncate) and the squared differences are summed as integers by
+p2p_psnr_sse, so the result equals the reference's for every image of a batch at once.
+save_checkpoint() / load_checkpoint(): the dictionary train.py:514-526 writes (`epoch`, `state_dict_g`,
+`state_dict_c`; the optimizer / scheduler entries are commented out in the reference and optional here).  The
+modules of this package have the reference's state_dict keys, so files interchange in both directions.
+"""
+from __future__ import annotations
+
+import os
+from typing import Optional
+
+import torch
+
+from . import _lib as L
+
+
+def psnr(ground: torch.Tensor, compressed: torch.Tensor) -> torch.Tensor:
+    """PSNR in dB of every image pair of two [B,3,H,W] (or [3,H,W]) fp32 CUDA tensors in [0,1] units; float64 [B].
+    Identical images give +inf (the reference's loop replaces that by 60.0, train.py:482-484)."""
+    L.require_cuda(ground, "psnr input")
+    L.require_cuda(compressed, "psnr input")
+    if ground.shape != compressed.shape:
+        raise L.P2PError("psnr needs two tensors of the same shape")
+    if ground.dim() == 3:
+        ground, compressed = ground[None], compressed[None]
+    B = ground.shape[0]
+    per_image = ground[0].numel()
+    a = ground.detach().contiguous().float()
+    b = compressed.detach().contiguous().float()
+    sse = torch.zeros(B, dtype=torch.int64, device=a.device)          # read by the kernel as uint64
+    L.call("p2p_psnr_sse", L.ptr(a), L.ptr(b), L.ptr(sse), B, per_image)
+    mse = sse.double() / float(per_image)
+    return 10.0 * torch.log10(255.0 ** 2 / mse)
+
+
+def save_checkpoint(path: str, epoch: int, net_g, net_c, **extra) -> None:
+    """torch.save of the reference's state dictionary (train.py:514-526): epoch + 1, state_dict_g, state_dict_c."""
+    state = {"epoch": epoch + 1, "state_dict_g": net_g.state_dict(), "state_dict_c": net_c.state_dict()}
+    state.update(extra)
+    d = os.path.dirname(path)
+    if d:
+        os.makedirs(d, exist_ok=True)
+    torch.save(state, path)
+
+
+def load_checkpoint(path: str, net_g, net_c=None, net_d=None, map_location: Optional[str] = None) -> int:
+    """Load a file written by the reference (or by save_checkpoint) and return its `epoch` (train.py:103-118 reads
+    the same keys; entries the file does not hold are skipped)."""
+    if not os.path.isfile(path):
+        raise FileNotFoundError(path)
+    state = torch.load(path, map_location=map_location, weights_only=False)
+    net_g.load_state_dict(state["state_dict_g"])
+    if net_c is not None and "state_dict_c" in state:
+        net_c.load_state_dict(state["state_dict_c"])
+    if net_d is not None and "state_dict_d" in state:
+        net_d.load_state_dict(state["state_dict_d"])
+    return int(state.get("epoch", 0))

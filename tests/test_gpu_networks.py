@@ -370,3 +370,22 @@ def test_full_iteration_with_phase3_matches_reference_golden(case):
     assert all(torch.equal(c0[k], v.detach()) for k, v in c.named_parameters())     # quirk Q3: net_c never moves
     assert int(g.state_dict()["in1_e.num_batches_tracked"]) == 2 * steps
     assert int(c.state_dict()["conv_block1.1.num_batches_tracked"]) == steps
+
+
+# ---- evaluation metric ---------------------------------------------------------------------------------
+def test_psnr_on_device_is_exact():
+    """p2p_psnr_sse against the oracle's numpy restatement and the vectors from the reference's own function."""
+    import p2p_pytorch_b200 as P
+    from oracle.make_golden_util import PSNR_CASES, psnr_inputs
+    gold = np.load(os.path.join(GOLD, "ref_psnr.npz"))
+    for name, h, w, seed, kind in PSNR_CASES:
+        a, b = psnr_inputs(h, w, seed, kind)
+        got = P.psnr(a.to(DEV), b.to(DEV)).item()
+        want = float(gold[name])
+        assert (np.isinf(got) and np.isinf(want)) or abs(got - want) <= 1e-12 * abs(want), (name, got, want)
+    # a batch at once == image by image
+    g = torch.Generator().manual_seed(9)
+    a, b = torch.rand(5, 3, 24, 40, generator=g), torch.rand(5, 3, 24, 40, generator=g) * 1.2 - 0.1
+    got = P.psnr(a.to(DEV), b.to(DEV)).cpu().numpy()
+    want = np.array([orc.psnr(a[i:i + 1], b[i:i + 1]) for i in range(5)])
+    assert np.allclose(got, want, rtol=1e-12, atol=0)

@@ -181,3 +181,45 @@ def test_oracle_full_iteration_with_phase3_matches_reference_golden(case):
                 _close(fingerprint(v.double())[:3], gold[p + "buf." + k][:3], 2e-4 * scale, 1e-3, p + k)
     assert all(torch.equal(c0[k], ot.c[k].detach()) for k in ot.c_trainable)
     assert int(ot.g["in1_e.num_batches_tracked"]) == 2 * steps
+
+
+# ---- evaluation metric and checkpoint format -----------------------------------------------------
+def test_oracle_psnr_matches_the_references_own_function():
+    """tests/golden/ref_psnr.npz was produced by executing the reference's tensor2img / psnr source unmodified
+    (oracle/make_golden_eval.py); the metric is integer work, so the oracle must reproduce it exactly."""
+    from oracle.make_golden_util import PSNR_CASES, psnr_inputs
+    gold = np.load(os.path.join(GOLD, "ref_psnr.npz"))
+    for name, h, w, seed, kind in PSNR_CASES:
+        a, b = psnr_inputs(h, w, seed, kind)
+        got, want = orc.psnr(a, b), float(gold[name])
+        assert (np.isinf(got) and np.isinf(want)) or got == want, (name, got, want)
+
+
+def test_checkpoint_files_interchange_with_the_reference(tmp_path):
+    """The dictionary of train.py:514-526 written from this package's modules loads (strict) into the reference's
+    modules and vice versa.  Needs /root/reference (build container); skipped elsewhere."""
+    import sys
+    if not os.path.isdir("/root/reference"):
+        pytest.skip("reference sources are not on this machine")
+    sys.path.insert(0, "/root/reference")
+    import networks as ref
+    import p2p_pytorch_b200 as P
+    g, c = P.ExpandNetwork(), P.CompressionNetwork()
+    g.load_state_dict(orc.init_g_state(123))
+    c.load_state_dict(orc.init_c_state(125))
+    path = str(tmp_path / "net_x_epoch_3.pth")
+    P.save_checkpoint(path, 3, g, c)
+    state = torch.load(path, weights_only=False)
+    assert set(state) == {"epoch", "state_dict_g", "state_dict_c"} and state["epoch"] == 4
+    rg, rc = ref.ExpandNetwork(), ref.CompressionNetwork()
+    rg.load_state_dict(state["state_dict_g"])          # strict
+    rc.load_state_dict(state["state_dict_c"])
+    # the other direction: a file as the reference writes it
+    path2 = str(tmp_path / "from_reference.pth")
+    torch.save({"epoch": 8, "state_dict_g": rg.state_dict(), "state_dict_c": rc.state_dict()}, path2)
+    g2, c2 = P.ExpandNetwork(), P.CompressionNetwork()
+    assert P.load_checkpoint(path2, g2, c2) == 8
+    for k, v in g.state_dict().items():
+        assert torch.equal(v, g2.state_dict()[k]), k
+    for k, v in c.state_dict().items():
+        assert torch.equal(v, c2.state_dict()[k]), k
