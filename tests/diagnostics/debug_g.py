@@ -1,9 +1,9 @@
 """Per-stage error growth of the generator (forward activations and backward gradients) against an fp32 torch
-graph on the same device.  Diagnostic only (not part of the product): python tools/debug_g.py [precision]"""
+graph on the same device.  Diagnostic only (not part of the product): python tests/diagnostics/debug_g.py [precision]"""
 import os
 import sys
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch
 import torch.nn.functional as F
 

@@ -1,6 +1,6 @@
 """Diagnostic: per-iteration difference between two eager runs, and between an eager and a graph-replayed run."""
 import os, sys
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch
 import p2p_pytorch_b200 as P
 from oracle import pix2pix_oracle as orc

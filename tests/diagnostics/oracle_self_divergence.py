@@ -1,7 +1,7 @@
 """How far do two runs of the ORACLE drift apart over 200 steps when the initial weights differ by 1e-6
 relative noise?  Calibrates the loss-curve tracking test (GAN dynamics amplify rounding differences)."""
 import os, sys
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np, torch
 from oracle import pix2pix_oracle as orc
 

@@ -2,7 +2,7 @@
 launched kernel by kernel, and the device-step Adam entry point against the host-step one.
 
 Trajectories cannot be compared: two EAGER runs from the same weights already drift apart (fp32 mode: losses
-1e-4, generator output 0.25 max after seven iterations at batch 2, 32x32 -- tools/graph_vs_eager.py) because
+1e-4, generator output 0.25 max after seven iterations at batch 2, 32x32 -- tests/diagnostics/graph_vs_eager.py) because
 the float atomics of the split-K weight gradients land in a different order each run and Adam's g/sqrt(v)
 amplifies that.  So every iteration is compared from the SAME state: before each step the eager twin loads the
 graphed trainer's weights, buffers and optimizer state, both take one step on the same batch, and outputs,

@@ -2,7 +2,7 @@
 C ABI) against the CPU oracle on the same seeded weights and inputs, plus the committed golden vectors that
 were generated from the unmodified reference.
 
-Tolerances, and where they come from (measured with tools/debug_g.py on a B200, batch 2, 32x32):
+Tolerances, and where they come from (measured with tests/diagnostics/debug_g.py on a B200, batch 2, 32x32):
   * every kernel alone meets 1e-5 (fp32) / 1e-2 (bf16, same rounded operands): tests/test_gpu_ops.py;
   * through the generator rounding differences grow ~x10 (24 conv+BatchNorm stages on random-init weights):
     fp32 mode 1.2e-6 after conv1 -> 1.6e-5 rms / 4.5e-5 max at the output; bf16 mode 0.44% -> 4.1% rms,
@@ -10,7 +10,7 @@ Tolerances, and where they come from (measured with tools/debug_g.py on a B200, 
     <= 2e-4 (max), bf16 mode <= 6e-2 rms and <= 0.2 max for the generator output, losses <= 5e-2 relative;
   * whole-network GRADIENTS are compared loosely: a forward difference of 1e-5 flips the ReLU/PReLU mask of
     an isolated element, and at these tiny map sizes (8x8x128 per image) one flipped element changes every
-    upstream gradient by ~1% rms (the jumps are visible per layer in tools/debug_g.py).  fp32: rms <= 5e-2;
+    upstream gradient by ~1% rms (the jumps are visible per layer in tests/diagnostics/debug_g.py).  fp32: rms <= 5e-2;
     bf16 (where ~1% of the masks flip per layer): cosine similarity >= 0.85.
 """
 import os
@@ -245,7 +245,7 @@ def test_loss_curves_track_oracle_200_steps():
     What "track" can mean is bounded by the reference's own sensitivity: two runs of the ORACLE whose initial
     weights differ by 1e-6 relative noise agree to 4 digits for ~10 steps and then drift apart by up to 38% in
     the 20-step means of loss_d (19% for loss_g) between steps 40 and 140 before re-converging
-    (tools/oracle_self_divergence.py -> profiles/oracle_self_divergence_200.npz): GAN dynamics at batch 2
+    (tests/diagnostics/oracle_self_divergence.py -> profiles/oracle_self_divergence_200.npz): GAN dynamics at batch 2
     amplify rounding differences.  So: pointwise agreement while the trajectories are still the same one,
     window means within 1.5x the oracle's own spread afterwards, and the same overall level."""
     steps = 200

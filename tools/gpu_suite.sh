@@ -18,9 +18,9 @@ for c in g_res g_conv2 g_conv1 g_deconv1 d_l0 d_l1_odd d_l3 d_l4 rect_odd; do
   stage "tc_$c" 180 python -m pytest tests/test_gpu_ops.py -q -x -k "test_conv_tcgen05_bf16 and $c"
 done
 stage tc_taken 180 python -m pytest tests/test_gpu_ops.py -q -x -k "path_is_taken"
-stage dbg_fp32 300 python tools/debug_g.py fp32
-stage dbg_bf16 300 python tools/debug_g.py bf16
-stage dbg_bf16simt 300 python tools/debug_g.py bf16-simt
+stage dbg_fp32 300 python tests/diagnostics/debug_g.py fp32
+stage dbg_bf16 300 python tests/diagnostics/debug_g.py bf16
+stage dbg_bf16simt 300 python tests/diagnostics/debug_g.py bf16-simt
 stage net_fp32 900 python -m pytest tests/test_gpu_networks.py -q --maxfail=40 -k "fp32 or drop_in or state_dict"
 stage net_bf16simt 600 python -m pytest tests/test_gpu_networks.py -q --maxfail=40 -k "bf16-simt"
 stage net_bf16 600 python -m pytest tests/test_gpu_networks.py -q --maxfail=40 -k "bf16 and not simt"
