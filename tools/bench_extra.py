@@ -48,4 +48,15 @@ for B in (4, 8):
     ms = timed(lambda: tr.step(a, b, c), 10, warmup=4)
     out[f"train_b{B}_512"] = {"ms_per_step": ms, "images_per_s": B / ms * 1e3}
     del tr
+# the iteration as the reference executes it: front end + G/D phases + phase 3, 16 x 256^2
+with contextlib.redirect_stdout(sys.stderr):
+    c = P.define_C("normal", 0.02, gpu_id=dev)
+c.train()
+tr = P.Pix2PixTrainer(g, d, cuda_graph=True, net_c=c)
+a = torch.rand(16, 3, 256, 256, device=dev, generator=gen) * 2 - 1
+b = torch.rand(16, 3, 256, 256, device=dev, generator=gen) * 2 - 1
+ms = timed(lambda: tr.step_full(a, b), 20, warmup=4)
+out["train_full_b16_256"] = {"ms_per_step": ms, "images_per_s": 16 / ms * 1e3}
+ms = timed(lambda: c.front_end(b), 20)
+out["front_end_b16_256"] = {"ms": ms}
 print(json.dumps(out))
