@@ -136,16 +136,41 @@ class Pix2PixTrainer:
         (num_batches_tracked advances by 2 per iteration) and the value of loss_c."""
         if self.net_c is None:
             raise ValueError("step_full needs the compression network: Pix2PixTrainer(..., net_c=define_C(...))")
+        if not self.cuda_graph:
+            return self._step_full_eager(real_a.cuda(non_blocking=True), real_b.cuda(non_blocking=True), phase3)
+        key = ("full", tuple(real_a.shape), tuple(real_b.shape), bool(phase3), E.get_precision())
+        rec = self._graphs.get(key)
+        if rec is None:
+            if self._eager_calls < self.graph_warmup:
+                self._eager_calls += 1
+                return self._step_full_eager(real_a.cuda(non_blocking=True), real_b.cuda(non_blocking=True), phase3)
+            from . import _lib as L
+            dev = self.optimizer_g.flat_p.device
+            inputs = [torch.empty(t.shape, dtype=torch.float32, device=dev) for t in (real_a, real_b)]
+            for dst, src in zip(inputs, (real_a, real_b)):
+                dst.copy_(src, non_blocking=True)
+            graph = torch.cuda.CUDAGraph()
+            torch.cuda.synchronize()
+            before = L.launch_count()
+            with torch.cuda.graph(graph):
+                outputs = self._step_full_eager(inputs[0], inputs[1], phase3)
+            self.graph_launches = L.launch_count() - before
+            rec = self._graphs[key] = {"graph": graph, "inputs": inputs, "outputs": outputs}
+        for dst, src in zip(rec["inputs"], (real_a, real_b)):
+            dst.copy_(src, non_blocking=True)
+        rec["graph"].replay()
+        return rec["outputs"]
+
+    def _step_full_eager(self, real_a, real_b, phase3):
         from . import _lib as L
-        real_b_dev = real_b.cuda(non_blocking=True) if not real_b.is_cuda else real_b
-        compressed = self.net_c.front_end(real_b_dev, 3)                                  # :297 (train-mode BatchNorm)
-        out = dict(self.step(real_a, real_b_dev, compressed))                             # :300-390
+        compressed = self.net_c.front_end(real_b, 3)                                      # :297 (train-mode BatchNorm)
+        out = dict(self._step_eager(real_a, real_b, compressed))                          # :300-390
         out["compressed"] = compressed
         if phase3:
             with torch.no_grad():
                 fake_after = self.net_g(compressed)                                       # :392
                 loss_c = torch.zeros((), dtype=torch.float32, device=compressed.device)
-                L.call("p2p_mse_pair_fwd", L.ptr(fake_after), L.ptr(real_b_dev.contiguous().float()), 1.0,
+                L.call("p2p_mse_pair_fwd", L.ptr(fake_after), L.ptr(real_b.contiguous().float()), 1.0,
                        L.ptr(loss_c), fake_after.numel())                                 # :394
             out["loss_c"] = loss_c
         return out

@@ -341,9 +341,11 @@ def test_define_c_is_a_drop_in():
 from oracle.make_golden_util import P3_CASES, fingerprint as _fp  # noqa: E402
 
 
+@pytest.mark.parametrize("graph", [False, True], ids=["eager", "graph"])
 @pytest.mark.parametrize("case", P3_CASES, ids=[c[0] for c in P3_CASES])
-def test_full_iteration_with_phase3_matches_reference_golden(case):
-    """fp32 mode against vectors from the unmodified reference modules (oracle/make_golden_p3.py)."""
+def test_full_iteration_with_phase3_matches_reference_golden(case, graph):
+    """fp32 mode against vectors from the unmodified reference modules (oracle/make_golden_p3.py); with graph=True
+    the second iteration is recorded into, and replayed from, a CUDA graph."""
     import p2p_pytorch_b200 as P
     name, batch, h, w, steps, seed = case
     gold = np.load(os.path.join(GOLD, f"ref_full_{name}.npz"))
@@ -352,7 +354,7 @@ def test_full_iteration_with_phase3_matches_reference_golden(case):
     c.load_state_dict(orc.init_c_state(125))
     c.train()
     c0 = {k: v.detach().clone() for k, v in c.named_parameters()}
-    tr = P.Pix2PixTrainer(g, d, net_c=c)
+    tr = P.Pix2PixTrainer(g, d, net_c=c, cuda_graph=graph, graph_warmup=1)
     for it in range(steps):
         a, b, _ = orc.synthetic_batch(batch, h, w, seed + it)
         out = tr.step_full(a.to(DEV), b.to(DEV))
