@@ -9,8 +9,10 @@ A "step" is one iteration of the reference's training loop body (train.py:294-39
 on one synthetic batch (16 images of 256x256 per GPU: BASELINE.json configs[1]; data parallel with a
 bucketed NCCL gradient all-reduce for N > 1, weak scaling).  Rank 0 prints ONE JSON line.
 
---impl reference times the CPU oracle (the reference's computation restated in fp32 PyTorch; the
-reference's own files cannot travel to the GPU box) on the host cores, batch 1 per step.
+--impl reference times the reference's OWN modules (oracle/_ref/networks.py, an unmodified copy made by
+oracle/build_ref.py in the build container; define_G / define_D / GANLoss through the loop body of
+train.py:294-390, VGG term off) on the host cores at the same batch size; if that copy is absent it falls back to the
+CPU oracle ("port").  --mode infer measures BASELINE.json configs[4]: generator-only inference (test.py:37-41).
 """
 import argparse
 import json
@@ -27,7 +29,7 @@ import torch  # noqa: E402
 
 RES_CONV_DRAM_BYTES = 18.19e6      # dram__bytes_read.sum + dram__bytes_write.sum of one residual-conv launch (profiles/r01d_ncu_res_fwd.md)
 FLOP_PER_IMG_256 = 173.41e9          # necessary conv FLOPs of one training step per image
-METRIC = "pix2pix 256x256 train images/sec"
+G_FWD_FLOP_PER_IMG_256 = 32.879e9    # generator forward alone
 
 
 def load_peaks():
@@ -84,33 +86,101 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+class ReferenceStep:
+    """The reference's iteration on the host cores: its own modules when oracle/_ref/networks.py is present
+    (kind "reference"), else the oracle's restatement (kind "port")."""
+
+    def __init__(self, size, batch):
+        from oracle import pix2pix_oracle as orc
+        from oracle.build_ref import load_reference_networks
+        import contextlib
+        self.orc, self.size, self.batch = orc, size, batch
+        ref = load_reference_networks()
+        self.kind = "reference" if ref is not None else "port"
+        if ref is None:
+            self.tr = orc.OracleTrainer(orc.init_g_state(123), orc.init_d_state(124))
+            return
+        torch.manual_seed(123)
+        with contextlib.redirect_stdout(sys.stderr):
+            self.net_g = ref.define_G("normal", 0.02, gpu_id="cpu")
+            self.net_d = ref.define_D(6, 64, gpu_id="cpu")
+        self.crit_gan = ref.GANLoss(tensor=torch.FloatTensor)     # the default tensor type needs CUDA (networks.py:810)
+        self.crit_feat = torch.nn.L1Loss()
+        self.opt_g = torch.optim.Adam(self.net_g.parameters(), lr=2e-4, betas=(0.5, 0.999))     # train.py:241-242
+        self.opt_d = torch.optim.Adam(self.net_d.parameters(), lr=2e-4, betas=(0.5, 0.999))
+        self.net_g.train(); self.net_d.train()
+
+    def infer(self, x):
+        if self.kind == "port":
+            return self.orc.g_forward(self.tr.g, x, False)
+        self.net_g.eval()
+        with torch.no_grad():
+            return self.net_g(x)                                                          # test.py:41
+
+    def step(self, real_a, real_b, compressed):
+        if self.kind == "port":
+            return self.tr.step(real_a, real_b, compressed)
+        net_g, net_d = self.net_g, self.net_d
+        fake_b = net_g(compressed.detach())                                               # train.py:300
+        pred_fake = net_d.forward(torch.cat((real_a, fake_b.detach()), 1))                # :308-309
+        loss_d_fake = self.crit_gan(pred_fake, False)                                     # :310
+        pred_real = net_d.forward(torch.cat((real_a, real_b.detach()), 1))                # :315-316
+        loss_d = (loss_d_fake + self.crit_gan(pred_real, True)) * 0.5                     # :317-320
+        pred_fake = net_d.forward(torch.cat((real_a, fake_b), 1))                         # :336-337
+        loss_g = self.crit_gan(pred_fake, True)                                           # :338
+        for i in range(3):                                                                # :344-351
+            for j in range(len(pred_fake[i]) - 1):
+                loss_g = loss_g + (1.0 / 3) * (4.0 / 4) * self.crit_feat(pred_fake[i][j], pred_real[i][j].detach()) * 10.0
+        loss_g = loss_g + torch.mean(torch.abs(fake_b[:, :, :, :-1] - fake_b[:, :, :, 1:])) \
+            + torch.mean(torch.abs(fake_b[:, :, :-1, :] - fake_b[:, :, 1:, :]))            # :123-126, :378-380
+        self.opt_g.zero_grad(); loss_g.backward(); self.opt_g.step()                      # :384-386
+        self.opt_d.zero_grad(); loss_d.backward(); self.opt_d.step()                      # :388-390
+        return {"loss_d": loss_d.detach(), "loss_g": loss_g.detach()}
+
+
+def workload_name(args):
+    S, B = args.size, args.batch
+    if args.mode == "infer":
+        return f"pix2pix {S}x{S} generator-only inference (test.py:37-41: net_g(input), eval mode, no autograd), {B} images per GPU"
+    vgg = "VGG19 perceptual term on" if args.with_vgg else "VGG term off"
+    return f"pix2pix {S}x{S} RGB->RGB training step (train.py:294-390, {vgg}), {B} images per GPU"
+
+
 def run_reference(args, rank, world):
-    """CPU oracle, all host threads, batch 1 per step (a bounded sample of the 16-image workload)."""
+    """The reference's CPU implementation, all host threads, one full batch per step."""
     if rank != 0:
         return
-    from oracle import pix2pix_oracle as orc
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
-    S = args.size
-    tr = orc.OracleTrainer(orc.init_g_state(123), orc.init_d_state(124))
-    batches = [orc.synthetic_batch(1, S, S, 500 + i) for i in range(2)]
+    S, B = args.size, args.batch
+    from oracle import pix2pix_oracle as orc
+    ref = ReferenceStep(S, B)
+    batches = [orc.synthetic_batch(B, S, S, 500 + i) for i in range(2)]
+    fn = (lambda bt: ref.infer(bt[2])) if args.mode == "infer" else (lambda bt: ref.step(*bt))
     for i in range(args.warmup):
-        tr.step(*batches[i % 2])
+        fn(batches[i % 2])
     t0 = time.perf_counter()
     for i in range(args.steps):
-        tr.step(*batches[i % 2])
+        fn(batches[i % 2])
     dt = time.perf_counter() - t0
-    ips = args.steps / dt
-    line = {"metric": METRIC, "value": ips, "unit": "images/s", "n_gpus": args.gpus, "steps": args.steps,
+    ips = B * args.steps / dt
+    what = ("the reference's own networks.py (oracle/_ref, unmodified)" if ref.kind == "reference"
+            else "the oracle (fp32 PyTorch restatement)")
+    line = {"metric": metric_name(args), "value": ips, "unit": "images/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": "reference",
-            "config": {"workload": f"pix2pix {S}x{S} RGB->RGB training step (train.py:294-390, VGG term off), "
-                                   f"{args.batch} images per GPU", "image": S, "batch_per_gpu": args.batch},
-            "cpu_baseline": {"value": ips, "unit": "images/s", "cores": cores, "kind": "port",
-                             "sample": f"batch 1 of the {args.batch}-image step, {args.steps} steps, "
+            "config": {"workload": workload_name(args), "image": S, "batch_per_gpu": B, "global_batch": B},
+            "cpu_baseline": {"value": ips, "unit": "images/s", "cores": cores, "kind": ref.kind,
+                             "sample": f"{args.steps} steps of the whole {B}-image batch through {what}, "
                                        f"torch {torch.__version__} fp32 CPU, {cores} threads"},
             "e2e": {"value": ips, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit(line)
+
+
+def metric_name(args):
+    if args.mode == "infer":
+        return f"pix2pix {args.size}x{args.size} generator inference images/sec"
+    return f"pix2pix {args.size}x{args.size} train images/sec"
 
 
 _REAL_STDOUT = None
@@ -166,6 +236,21 @@ def time_dominant_kernel(P, B, S, iters=20):
     return ms, flops
 
 
+def h2d_probe(dev, mb=64, reps=5):
+    """GB/s of a pinned host -> device copy on an otherwise idle GPU (the box's PCIe / IOMMU path, for the e2e line)"""
+    src = torch.empty(mb << 20, dtype=torch.uint8).pin_memory()
+    dst = torch.empty(mb << 20, dtype=torch.uint8, device=dev)
+    dst.copy_(src, non_blocking=True)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        dst.copy_(src, non_blocking=True)
+    e1.record()
+    torch.cuda.synchronize()
+    return reps * (mb << 20) / (e0.elapsed_time(e1) * 1e-3) / 1e9
+
+
 def run_ours(args, rank, world, local_rank):
     import torch.distributed as dist
     import p2p_pytorch_b200 as P
@@ -173,6 +258,7 @@ def run_ours(args, rank, world, local_rank):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     B, S = args.batch, args.size
+    infer = args.mode == "infer"
     P.set_precision(args.precision)
     torch.manual_seed(123)                                   # the reference's default --seed (train.py:155)
     torch.cuda.manual_seed(123)
@@ -183,15 +269,12 @@ def run_ours(args, rank, world, local_rank):
     tr = P.Pix2PixTrainer(g, d, cuda_graph=not args.no_graph)
     tr.broadcast_parameters(0)
 
-    # synthetic pairs generated on the device: real_a, real_b ~ U(-1,1), G input = 3-bit quantised real_b
+    # synthetic pairs generated on the device as 8-bit images (what dataset.py decodes from disk); the iteration turns
+    # them into real_a, real_b in [-1,1] (ToTensor + Normalize) and the 3-bit generator input on the device
     gen = torch.Generator(device=dev).manual_seed(123 + rank)
     n_sets = 2
-    data = []
-    for _ in range(n_sets):
-        a = torch.rand(B, 3, S, S, device=dev, generator=gen) * 2 - 1
-        b = torch.rand(B, 3, S, S, device=dev, generator=gen) * 2 - 1
-        c = torch.round((b * 0.5 + 0.5).clamp(0, 1) * 7) / 7
-        data.append((a, b, c))
+    data = [tuple(torch.randint(0, 256, (B, 3, S, S), device=dev, generator=gen, dtype=torch.uint8) for _ in range(2))
+            for _ in range(n_sets)]
 
     def barrier():
         if world > 1:
@@ -205,12 +288,50 @@ def run_ours(args, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return t.item()
 
+    if infer:
+        # config 5: net_g(input) in eval mode under no_grad (test.py:37-41), replayed from a CUDA graph; the 8-bit
+        # input is decoded on the device, the fp32 output image goes back to the host in the e2e leg
+        g.eval()
+        x8 = torch.empty(B, 3, S, S, dtype=torch.uint8, device=dev)
+        x32 = torch.empty(B, 3, S, S, dtype=torch.float32, device=dev)
+
+        def infer_body():
+            P._lib.call("p2p_decode_u8", x8.data_ptr(), x32.data_ptr(), None, x8.numel(), 3)
+            return g(x32)
+        x8.copy_(data[0][1])
+        with torch.no_grad():
+            for _ in range(2):
+                y = infer_body()
+            graph = None
+            n_rec = 0
+            if not args.no_graph:
+                torch.cuda.synchronize()
+                graph = torch.cuda.CUDAGraph()
+                l0 = P._lib.launch_count()
+                with torch.cuda.graph(graph):
+                    y = infer_body()
+                n_rec = P._lib.launch_count() - l0
+
+        def step_dev(i):
+            x8.copy_(data[i % n_sets][1], non_blocking=True)
+            if graph is not None:
+                graph.replay()
+                return {"y": y}
+            with torch.no_grad():
+                return {"y": infer_body()}
+        graph_launches = n_rec
+    else:
+        def step_dev(i):
+            return tr.step(*data[i % n_sets])
+
     for i in range(args.warmup):
-        tr.step(*data[i % n_sets])
+        step_dev(i)
     primed = 0
-    while tr.cuda_graph and not tr._graphs:                  # --warmup below 3: record the graph outside the timed region
-        tr.step(*data[primed % n_sets])
+    while not infer and tr.cuda_graph and not tr._graphs:    # --warmup below 3: record the graph outside the timed region
+        step_dev(primed)
         primed += 1
+    if not infer:
+        graph_launches = tr.graph_launches
     # ---- device-resident timing ---------------------------------------------------------------
     sampler = ClockSampler(local_rank)
     if rank == 0:
@@ -220,70 +341,121 @@ def run_ours(args, rank, world, local_rank):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for i in range(args.steps):
-        out = tr.step(*data[i % n_sets])
+        out = step_dev(i)
     e1.record()
     barrier()
     ms = max_over_ranks(e0.elapsed_time(e1))
     launches = P._lib.launch_count() - l0
-    if tr.cuda_graph:                                        # replayed launches do not pass through the C ABI's counter
-        launches = tr.graph_launches * args.steps
+    if not args.no_graph:                                    # replayed launches do not pass through the C ABI's counter
+        launches = graph_launches * args.steps
     clocks = sampler.stop() if rank == 0 else None
     value = world * B * args.steps / (ms * 1e-3)
 
-    # ---- end to end: pinned host inputs -> H2D -> step -> D2H of the losses, every step ---------
+    # ---- end to end: pinned host bytes -> H2D -> step -> D2H of the result, every step -----------------
+    probe_gbs = h2d_probe(dev)
     host = [tuple(t.cpu().pin_memory() for t in s) for s in data]
-    dbuf = tuple(torch.empty_like(t) for t in data[0])
-    loss_host = torch.empty(2, dtype=torch.float32).pin_memory()
-    def e2e_step(i):
-        if tr.cuda_graph:                                    # step() itself copies host inputs into the graph's buffers
-            return tr.step(*host[i % n_sets])
-        for dst, src in zip(dbuf, host[i % n_sets]):
-            dst.copy_(src, non_blocking=True)
-        return tr.step(*dbuf)
+    if infer:
+        y_host = torch.empty(B, 3, S, S, dtype=torch.float32).pin_memory()
+        h2d, d2h = x8.numel(), y_host.numel() * 4
+        copy_stream = torch.cuda.Stream(device=dev)
+        stage = [torch.empty_like(x8) for _ in range(2)]
+        staged_ev = [torch.cuda.Event() for _ in range(2)]
+        free_ev = [torch.cuda.Event() for _ in range(2)]
 
-    for i in range(2):
-        e2e_step(i)
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    if tr.cuda_graph:
-        tr.prefetch(*host[0])                                # inside the timed region, like every later H2D copy
-    for i in range(args.steps):
-        o = e2e_step(i)
-        if tr.cuda_graph and i + 1 < args.steps:
-            tr.prefetch(*host[(i + 1) % n_sets])             # the next batch travels while this iteration runs
-        loss_host.copy_(torch.stack((o["loss_d"], o["loss_g"])), non_blocking=True)
-        torch.cuda.current_stream().synchronize()       # the caller reads the losses every iteration
-    e1.record()
-    barrier()
-    ms_e2e = max_over_ranks(e0.elapsed_time(e1))
-    e2e = world * B * args.steps / (ms_e2e * 1e-3)
-    h2d = sum(t.numel() * 4 for t in host[0])
+        def stage_in(i):                                     # H2D of batch i on the copy stream (double-buffered)
+            sl = i % 2
+            copy_stream.wait_event(free_ev[sl])
+            with torch.cuda.stream(copy_stream):
+                stage[sl].copy_(host[i % n_sets][1], non_blocking=True)
+                staged_ev[sl].record(copy_stream)
+
+        def e2e_step(i, prefetch=True):
+            cur = torch.cuda.current_stream()
+            sl = i % 2
+            if prefetch:
+                cur.wait_event(staged_ev[sl])
+                x8.copy_(stage[sl], non_blocking=True)
+                free_ev[sl].record(cur)
+            else:
+                x8.copy_(host[i % n_sets][1], non_blocking=True)
+            if graph is not None:
+                graph.replay()
+                yy = y
+            else:
+                with torch.no_grad():
+                    yy = infer_body()
+            y_host.copy_(yy, non_blocking=True)
+            return yy
+        for ev in free_ev:
+            ev.record(torch.cuda.current_stream())
+    else:
+        loss_host = torch.empty(2, dtype=torch.float32).pin_memory()
+        h2d, d2h = sum(t.numel() for t in host[0]), 8
+
+        def stage_in(i):
+            tr.prefetch(*host[i % n_sets])
+
+        def e2e_step(i, prefetch=True):
+            o = tr.step(*host[i % n_sets])                   # copies (or picks up the prefetched copy of) the host batch
+            loss_host.copy_(torch.stack((o["loss_d"], o["loss_g"])), non_blocking=True)
+            return o
+
+    def e2e_run(prefetch):
+        use_pf = prefetch and (infer or tr.cuda_graph)
+        for i in range(2):
+            if use_pf:
+                stage_in(i)
+            e2e_step(i, use_pf)
+            torch.cuda.current_stream().synchronize()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        if use_pf:
+            stage_in(0)                                      # inside the timed region, like every later H2D copy
+        for i in range(args.steps):
+            e2e_step(i, use_pf)
+            if use_pf and i + 1 < args.steps:
+                stage_in(i + 1)                              # the next batch travels while this iteration runs
+            torch.cuda.current_stream().synchronize()        # the caller reads the result every iteration
+        e1.record()
+        barrier()
+        ms_e = max_over_ranks(e0.elapsed_time(e1))
+        return world * B * args.steps / (ms_e * 1e-3), ms_e / args.steps
+
+    e2e_serial, ms_serial = e2e_run(False)
+    e2e, ms_e2e = e2e_run(True)
 
     if rank != 0:
         return
     hbm, tf_burst, tf_sust, which = load_peaks()
-    line = {"metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
+    flop_img = (G_FWD_FLOP_PER_IMG_256 if infer else FLOP_PER_IMG_256) * (S / 256.0) ** 2
+    line = {"metric": metric_name(args), "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16" if args.precision.startswith("bf16") else "f32", "data": "synthetic",
-            "config": {"workload": f"pix2pix {S}x{S} RGB->RGB training step (train.py:294-390, VGG term off), "
-                                   f"{B} images per GPU", "image": S, "batch_per_gpu": B, "global_batch": B * world,
+            "config": {"workload": workload_name(args), "image": S, "batch_per_gpu": B, "global_batch": B * world,
                        "parallelism": f"dp{world}", "precision": P.get_precision(),
-                       "launch": (f"one CUDA graph replay per step ({tr.graph_launches} kernels of libp2p_b200.so recorded)"
-                                  if tr.cuda_graph else "kernel-by-kernel launches"),
+                       "input": "8-bit RGB pairs, decoded (ToTensor + Normalize) and 3-bit quantised on the device",
+                       "launch": (f"one CUDA graph replay per step ({graph_launches} kernels of libp2p_b200.so recorded)"
+                                  if not args.no_graph else "kernel-by-kernel launches"),
                        "l2": "per-step working set (>1 GB of activations) exceeds the 126 MB L2; no explicit flush"},
             "clocks": clocks,
-            "e2e": {"value": e2e, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8},
+            "e2e": {"value": e2e, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": ms_e2e,
+                    # diagnosis of the end-to-end leg: the same loop without the prefetch overlap, and the bandwidth
+                    # of a pinned 64 MB host->device copy on the idle GPU (this box's PCIe / IOMMU path)
+                    "no_prefetch": {"value": e2e_serial, "ms_per_step": ms_serial},
+                    "h2d_probe_gbs": probe_gbs},
             "gpu_launches": launches,
-            "step_tensor_frac": value / world * FLOP_PER_IMG_256 * (S / 256.0) ** 2 / (tf_sust * 1e12),
-            "final_losses": {"loss_d": out["loss_d"].item(), "loss_g": out["loss_g"].item()}}
+            "step_tensor_frac": value / world * flop_img / (tf_sust * 1e12)}
+    if not infer:
+        line["final_losses"] = {"loss_d": out["loss_d"].item(), "loss_g": out["loss_g"].item()}
     try:
         kms, kflops = time_dominant_kernel(P, B, S)
         ach = kflops / (kms * 1e-3) / 1e12
         line["roofline"] = {"bound": "tensor", "achieved": ach, "peak": tf_burst, "unit": "TFLOP/s",
                             "frac": ach / tf_burst,
                             # dram__bytes_read.sum + dram__bytes_write.sum of this launch, ncu --set full
-                            # (profiles/r01c_ncu_dominant_kernels.md); valid for the default B=16, 256x256 shape only
+                            # (profiles/); valid for the default B=16, 256x256 shape only
                             "traffic": RES_CONV_DRAM_BYTES if (B == 16 and S == 256) else None, "peak_source": which,
                             "kernel": "conv_halo_swap_kernel<64> (3x3 128->128 residual conv fwd, bf16, fp32 accumulate)",
                             "ms_per_launch": kms}
@@ -291,21 +463,24 @@ def run_ours(args, rank, world, local_rank):
         line["roofline"] = {"bound": "tensor", "achieved": None, "peak": tf_burst, "unit": "TFLOP/s", "frac": None,
                             "traffic": None, "note": f"dominant-kernel timing unavailable: {e}"}
     if world == 1 and not args.no_cpu_baseline:
-        from oracle import pix2pix_oracle as orc             # the CPU checker, timed as the reported baseline only
+        # the reference's CPU implementation (or, without oracle/_ref, the CPU checker), timed as the reported baseline
+        from oracle import pix2pix_oracle as orc
         cores = os.cpu_count() or 1
         torch.set_num_threads(cores)
-        otr = orc.OracleTrainer(orc.init_g_state(123), orc.init_d_state(124))
-        ob = orc.synthetic_batch(1, S, S, 77)
-        for _ in range(2):
-            otr.step(*ob)
-        n = 10
-        t0 = time.perf_counter()
-        for _ in range(n):
-            otr.step(*ob)
+        ref = ReferenceStep(S, B)
+        ob = orc.synthetic_batch(B, S, S, 77)
+        fn = (lambda: ref.infer(ob[2])) if infer else (lambda: ref.step(*ob))
+        fn()
+        n, t0 = 0, time.perf_counter()
+        while n < 2 or (time.perf_counter() - t0 < 12.0 and n < 10):
+            fn()
+            n += 1
         dt = time.perf_counter() - t0
-        line["cpu_baseline"] = {"value": n / dt, "unit": "images/s", "cores": cores, "kind": "port",
-                                "sample": f"{n} steps at batch 1 ({S}x{S}) of the oracle (fp32 PyTorch restatement "
-                                          f"of train.py:294-390), 2 warm-up steps, {cores} threads"}
+        line["cpu_baseline"] = {"value": B * n / dt, "unit": "images/s", "cores": cores, "kind": ref.kind,
+                                "sample": f"{n} steps of the whole {B}-image batch ({S}x{S}) through "
+                                          + ("the reference's own networks.py (oracle/_ref)" if ref.kind == "reference"
+                                             else "the oracle (fp32 PyTorch restatement of train.py:294-390)")
+                                          + f", 1 warm-up step, {cores} threads"}
     emit(line)
 
 
@@ -318,6 +493,9 @@ def main():
     ap.add_argument("--batch", type=int, default=16, help="images per GPU")
     ap.add_argument("--size", type=int, default=256)
     ap.add_argument("--precision", default="bf16", choices=["bf16", "bf16-simt", "fp32"])
+    ap.add_argument("--mode", default="train", choices=["train", "infer"],
+                    help="infer: generator-only inference (BASELINE.json configs[4]; use --batch 64)")
+    ap.add_argument("--with-vgg", action="store_true", help="include the VGG19 perceptual term (train.py:377)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch kernel by kernel instead of replaying a CUDA graph")
     args = ap.parse_args()

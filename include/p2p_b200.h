@@ -62,6 +62,12 @@ const char* p2p_last_error(void);
 int p2p_device_supports_tc(void);
 /* number of kernels this library has enqueued in this process so far (bench.py's gpu_launches). */
 long long p2p_launch_count(void);
+/* Diagnostics: between p2p_trace_begin() and p2p_trace_end() every convolution entry point appends one line naming
+ * the kernel instantiation (and its block geometry) that served the call; p2p_trace_end copies the text into `buf`
+ * (at most cap-1 bytes, NUL-terminated) and returns the size needed.  Tests use it to show that the shapes they
+ * check run on the same instantiations as the benchmark.  No reference counterpart. */
+void p2p_trace_begin(void);
+int p2p_trace_end(char* buf, int cap);
 
 /* ---- convolutions: replace nn.Conv2d fwd/bwd (reference networks.py:400,404 ConvLayer;
  *      :416,422 UpsampleConvLayer; :766-784 NLayerDiscriminator) ------------------------- */
@@ -226,6 +232,12 @@ int p2p_kx_scatter(const void* dy, void* a, int N, int H, int Wo, int Wa, int kw
  * generate_dataset.py:29-34 does for train.py:297, to `compressed` (may be NULL); both NCHW fp32 [B,3,H,W]. */
 int p2p_c_output(const void* res, const float* x, float* y, float* compressed, int B, int H, int W, int bits, int dtype,
                  void* stream);
+/* 8-bit images -> the fp32 tensors of the iteration: dst = (src / 255 - 0.5) / 0.5, i.e. ToTensor + Normalize(0.5, 0.5)
+ * of dataset.py:19-20,30-40 with torchvision's fp32 operation order (bit-identical), and, when `quant` is not NULL,
+ * quant = compress(dst * 0.5 + 0.5, bits) of generate_dataset.py:29-34 (the quantiser in front of the generator,
+ * train.py:297 without net_c) in the same pass.  n elements, any layout; buffers 16-byte aligned.  Lets a host ship a
+ * batch as bytes (4x less host-to-device traffic than the fp32 tensors the reference's DataLoader hands over). */
+int p2p_decode_u8(const uint8_t* src, float* dst, float* quant, int64_t n, int bits, void* stream);
 /* stored map [B,H,W,C] dtype <-> NCHW fp32 [B,c_real,H,W] (drop-in API edge). */
 int p2p_nhwc_to_nchw(const void* in, float* out, int B, int H, int W, int C, int c_real, int dtype, void* stream);
 int p2p_nchw_to_nhwc(const float* in, void* out, int B, int H, int W, int C, int c_real, int dtype, void* stream);
@@ -267,6 +279,11 @@ int p2p_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float
  * torch/optim/adam.py).  Bias corrections are computed on the device in double precision. */
 int p2p_adam_step_dev(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
                       float eps, const int* step_dev, float grad_scale, void* stream);
+/* As p2p_adam_step_dev, with the learning rate and the gradient scale read from DEVICE memory as well
+ * (hyper_dev[0] = lr, hyper_dev[1] = grad_scale): the reference steps an LR scheduler every epoch
+ * (train.py:441-443, networks.py:104-125), and a launch replayed from a CUDA graph must see the new value. */
+int p2p_adam_step_graph(float* p, const float* g, float* m, float* v, int64_t n, float beta1, float beta2, float eps,
+                        const int* step_dev, const float* hyper_dev, void* stream);
 
 #ifdef __cplusplus
 }

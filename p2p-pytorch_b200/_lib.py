@@ -91,6 +91,7 @@ SIGNATURES = {
     "p2p_kx_gather_sum": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp],
     "p2p_kx_scatter": [_vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp],
     "p2p_c_output": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp],
+    "p2p_decode_u8": [_vp, _vp, _vp, _i64, _i, _vp],
     "p2p_nhwc_to_nchw": [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp],
     "p2p_nchw_to_nhwc": [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp],
     "p2p_mse_const_fwd": [_vp, _f, _f, _vp, _i64, _i, _i, _i, _vp],
@@ -108,9 +109,12 @@ SIGNATURES = {
     "p2p_sn_weight_grad_multi": [_i, _vp, _vp],
     "p2p_adam_step": [_vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _i, _f, _vp],
     "p2p_adam_step_dev": [_vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _vp, _f, _vp],
+    "p2p_adam_step_graph": [_vp, _vp, _vp, _vp, _i64, _f, _f, _f, _vp, _vp, _vp],
 }
 NOARG = {"p2p_version": C.c_int, "p2p_last_error": C.c_char_p, "p2p_device_supports_tc": C.c_int,
          "p2p_launch_count": C.c_longlong}
+# entry points that take no stream argument: name -> (argument ctypes, result ctype)
+MISC = {"p2p_trace_begin": ([], None), "p2p_trace_end": ([C.c_char_p, C.c_int], C.c_int)}
 
 _lib = None
 
@@ -129,8 +133,26 @@ def load() -> C.CDLL:
         for name, res in NOARG.items():
             fn = getattr(lib, name)
             fn.argtypes, fn.restype = [], res
+        for name, (args, res) in MISC.items():
+            fn = getattr(lib, name)
+            fn.argtypes, fn.restype = args, res
         _lib = lib
     return _lib
+
+
+def trace_begin() -> None:
+    """start recording which kernel instantiation serves each convolution call (p2p_trace_begin)"""
+    load().p2p_trace_begin()
+
+
+def trace_end():
+    """stop recording; returns the list of recorded lines"""
+    lib = load()
+    need = lib.p2p_trace_end(None, 0)
+    buf = C.create_string_buffer(max(need, 1))
+    # the trace is closed by the first call; the text stays until the next p2p_trace_begin
+    lib.p2p_trace_end(buf, need)
+    return [ln for ln in buf.value.decode().split("\n") if ln]
 
 
 def launch_count() -> int:

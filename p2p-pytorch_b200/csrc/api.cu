@@ -1,5 +1,8 @@
 // Library-level entry points and the convolution dispatch (tcgen05 path vs fp32-accumulate SIMT path).
 #include <atomic>
+#include <cstdarg>
+#include <cstring>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -9,6 +12,22 @@ static thread_local std::string g_last_error;
 void set_error(const std::string& s) { g_last_error = s; }
 static std::atomic<long long> g_launches{0};
 void count_launches(int n) { g_launches += n; }
+
+static std::mutex g_trace_mu;
+static std::atomic<bool> g_trace_on{false};
+static std::string g_trace;
+bool trace_open() { return g_trace_on.load(std::memory_order_relaxed); }
+void trace_kernel(const char* fmt, ...) {
+  if (!trace_open()) return;
+  char buf[256];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  std::lock_guard<std::mutex> lk(g_trace_mu);
+  g_trace += buf;
+  g_trace += '\n';
+}
 
 // conv_simt.cu
 int conv_fwd_simt(const p2p_conv* c, const void* in, const void* w, const float* bias, void* out, int dtype,
@@ -42,16 +61,16 @@ static int check_conv(const p2p_conv* c) {
   return 0;
 }
 
-static bool g_tc_checked = false, g_tc_ok = false;
+// compute capability 10.x of the CURRENT device, cached per ordinal (0 = not looked up yet, 1 = yes, 2 = no)
+static std::atomic<int> g_tc_state[kMaxDevices];
 static bool device_tc() {
-  if (!g_tc_checked) {
-    int dev = 0, major = 0;
-    if (cudaGetDevice(&dev) == cudaSuccess &&
-        cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) == cudaSuccess)
-      g_tc_ok = (major == 10);
-    g_tc_checked = true;
-  }
-  return g_tc_ok;
+  int dev = 0, major = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return false;
+  const bool cached = dev >= 0 && dev < kMaxDevices;
+  if (cached && g_tc_state[dev].load(std::memory_order_relaxed) != 0) return g_tc_state[dev].load() == 1;
+  const bool ok = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) == cudaSuccess && major == 10;
+  if (cached) g_tc_state[dev].store(ok ? 1 : 2);
+  return ok;
 }
 
 }  // namespace p2p
@@ -64,6 +83,23 @@ int p2p_version(void) { return 100; }
 const char* p2p_last_error(void) { return g_last_error.c_str(); }
 int p2p_device_supports_tc(void) { return device_tc() ? 1 : 0; }
 long long p2p_launch_count(void) { return g_launches.load(); }
+
+void p2p_trace_begin(void) {
+  std::lock_guard<std::mutex> lk(g_trace_mu);
+  g_trace.clear();
+  g_trace_on.store(true);
+}
+int p2p_trace_end(char* buf, int cap) {
+  std::lock_guard<std::mutex> lk(g_trace_mu);
+  g_trace_on.store(false);
+  const int need = (int)g_trace.size() + 1;
+  if (buf != nullptr && cap > 0) {
+    const int n = need <= cap ? need - 1 : cap - 1;
+    memcpy(buf, g_trace.data(), (size_t)n);
+    buf[n] = 0;
+  }
+  return need;
+}
 
 int p2p_conv_fwd(const p2p_conv* c, const void* in, const void* w_packed, const float* bias, void* out, double* stats,
                  int dtype, int impl, void* stream) {

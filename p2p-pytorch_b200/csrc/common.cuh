@@ -13,6 +13,29 @@ namespace p2p {
 
 void set_error(const std::string& s);
 void count_launches(int n);   // kernels enqueued so far (reported by bench.py as gpu_launches)
+// Which kernel instantiation served a call (p2p_trace_begin / p2p_trace_end): lets a test prove that the shapes it
+// checks run on the same instantiations as the benchmark.  A no-op unless a trace is open.
+void trace_kernel(const char* fmt, ...);
+bool trace_open();
+
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device attribute: remember the largest opt-in made for a
+// kernel on each device ordinal (a process may drive several GPUs through the C ABI).  Setting it twice is harmless,
+// so concurrent first calls need no lock.
+constexpr int kMaxDevices = 64;
+struct SmemOptIn {
+  int bytes[kMaxDevices] = {};
+};
+template <typename K>
+static inline cudaError_t ensure_dyn_smem(K kernel, SmemOptIn& cache, int smem) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= kMaxDevices || smem > cache.bytes[dev]) {
+    e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e == cudaSuccess && dev >= 0 && dev < kMaxDevices) cache.bytes[dev] = smem;
+  }
+  return e;
+}
 
 #define P2P_REQUIRE(cond, msg)                                            \
   do {                                                                    \

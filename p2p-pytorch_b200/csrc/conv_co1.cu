@@ -78,6 +78,7 @@ int conv_wgrad_co1(const p2p_conv* c, const void* in, const void* dout, float* a
   int64_t stripes = ((int64_t)c->N * c->Hi * c->Wi + ppb - 1) / ppb;
   if (stripes > kSMs) stripes = kSMs;
   const dim3 grid((int)stripes, (c->kh * c->kw + 3) / 4);
+  trace_kernel("conv_co1_wgrad");
   P2P_DISPATCH(dtype, conv_co1_wgrad_kernel<T><<<grid, 256, 0, st>>>((const T*)in, (const T*)dout, acc, c->N, c->Hi, c->Wi,
                                                                     c->Ci, c->Ho, c->Wo, c->kh, c->kw, c->pad););
   P2P_LAUNCH_CHECK();

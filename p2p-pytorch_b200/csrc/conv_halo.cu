@@ -259,7 +259,9 @@ __global__ void __launch_bounds__(224, 1)
 // bias and the BatchNorm sums are thread-local (no shared memory at all), and neighbouring lanes exchange one
 // value per pixel pair so that every lane stores 4 bytes and a warp covers 64 contiguous bytes of two pixels.
 // ---------------------------------------------------------------------------------------------------
-template <int CIN_BLK>
+// PROBE = true compiles in the clock64 / %globaltimer stamps read by tools/halo_clocks.py (a separate instantiation:
+// the production kernel contains none of it).
+template <int CIN_BLK, bool PROBE>
 __global__ void __launch_bounds__(352, 1)
     conv_halo_swap_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                           const __grid_constant__ HaloParams p) {
@@ -275,7 +277,9 @@ __global__ void __launch_bounds__(352, 1)
   __shared__ uint32_t tmem_base_s;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (p.clk != nullptr && threadIdx.x == 0) p.clk[blockIdx.x * 16 + 8] = (long long)gtimer();
+  const bool probe = PROBE && p.clk != nullptr;
+#define P2P_CLK() (PROBE ? clock64() : 0ll)
+  if (probe && threadIdx.x == 0) p.clk[blockIdx.x * 16 + 8] = (long long)gtimer();
   const int blocks_per_img = p.blocks_w * p.blocks_h;
   const int items_per_ntile = blocks_per_img * p.n_img;
   const int n_items = items_per_ntile * p.n_tiles;
@@ -336,21 +340,21 @@ __global__ void __launch_bounds__(352, 1)
     const uint32_t w_hi = desc_hi(8 * RB, RB);
     int ab = 0, bs = 0, li = 0;
     uint32_t aph = 0, bph = 0;
-    const long long c_tot = clock64();
+    const long long c_tot = P2P_CLK();
     long long c_te = 0, c_af = 0, c_t0;
-    if (p.clk != nullptr && lane == 0) p.clk[blockIdx.x * 16 + 9] = (long long)gtimer();
+    if (probe && lane == 0) p.clk[blockIdx.x * 16 + 9] = (long long)gtimer();
     for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++li) {
       const int set = li & 1;
-      c_t0 = clock64();
+      c_t0 = P2P_CLK();
       mbar_wait(&t_empty[set], ((li >> 1) & 1) ^ 1);
-      c_te += clock64() - c_t0;
+      c_te += P2P_CLK() - c_t0;
       tc_fence_after();
       const uint32_t acc = tmem_base + set * 256;
       uint32_t first = 0;
       for (int c = 0; c < p.c_chunks; ++c) {
-        c_t0 = clock64();
+        c_t0 = P2P_CLK();
         mbar_wait(&a_full[ab], aph);
-        c_af += clock64() - c_t0;
+        c_af += P2P_CLK() - c_t0;
         tc_fence_after();
         const uint32_t x_lo0 = desc_lo(smem_u32(sA + ab * p.a_bytes), 16);
         if (elect_one()) {
@@ -358,9 +362,9 @@ __global__ void __launch_bounds__(352, 1)
           uint32_t bph_l = bph;
           long long c_bf = 0;
           for (int t = 0; t < p.n_taps; ++t) {
-            const long long c_b0 = clock64();
+            const long long c_b0 = P2P_CLK();
             mbar_wait(&b_full[bs_l], bph_l);
-            c_bf += clock64() - c_b0;
+            c_bf += P2P_CLK() - c_b0;
             tc_fence_after();
             const uint32_t w_lo = desc_lo(smem_u32(sB + bs_l * W_BYTES), 16);
             const uint32_t x_lo = x_lo0 + (uint32_t)p.taps[t].row_off16;
@@ -370,7 +374,7 @@ __global__ void __launch_bounds__(352, 1)
             umma_commit(&b_empty[bs_l]);
             if (++bs_l == p.nb) { bs_l = 0; bph_l ^= 1; }
           }
-          if (p.clk != nullptr)
+          if (probe)
             atomicAdd(reinterpret_cast<unsigned long long*>(p.clk + blockIdx.x * 16 + 3), (unsigned long long)c_bf);
         }
         __syncwarp();
@@ -384,8 +388,8 @@ __global__ void __launch_bounds__(352, 1)
       if (elect_one()) umma_commit(&t_full[set]);
       __syncwarp();
     }
-    if (p.clk != nullptr && lane == 0) {
-      p.clk[blockIdx.x * 16 + 0] = clock64() - c_tot;
+    if (probe && lane == 0) {
+      p.clk[blockIdx.x * 16 + 0] = P2P_CLK() - c_tot;
       p.clk[blockIdx.x * 16 + 1] = c_te;
       p.clk[blockIdx.x * 16 + 2] = c_af;
       p.clk[blockIdx.x * 16 + 10] = (long long)gtimer();
@@ -429,9 +433,9 @@ __global__ void __launch_bounds__(352, 1)
       __nv_bfloat16* obase = p.epi.out + (int64_t)img * p.out_sN + n0 + (even ? ch : ch - 1) +
                              (int64_t)(ox0 * p.epi.w_mul + p.epi.w_off) * p.epi.out_sW + (even ? 0 : sx);
       const bool all_real_x = __all_sync(0xffffffffu, real && ox0 + 8 <= p.epi.Wv);
-      const long long c_e0 = clock64();
+      const long long c_e0 = P2P_CLK();
       mbar_wait(&t_full[set], (li >> 1) & 1);
-      const long long c_e1 = clock64();
+      const long long c_e1 = P2P_CLK();
       tc_fence_after();
       float s = 0.f, ss = 0.f;
       if (n_cols <= 0) {                         // blocks of 16 rows: the upper half has nothing to read
@@ -491,9 +495,9 @@ __global__ void __launch_bounds__(352, 1)
       }
       d_s += (double)s;
       d_ss += (double)ss;
-      if (p.clk != nullptr && threadIdx.x == 64) {
+      if (probe && threadIdx.x == 64) {
         p.clk[blockIdx.x * 16 + 5] += c_e1 - c_e0;
-        p.clk[blockIdx.x * 16 + 6] += clock64() - c_e1;
+        p.clk[blockIdx.x * 16 + 6] += P2P_CLK() - c_e1;
         p.clk[blockIdx.x * 16 + 11] = (long long)gtimer();
       }
     }
@@ -505,7 +509,8 @@ __global__ void __launch_bounds__(352, 1)
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, TMEM_COLS);
-  if (p.clk != nullptr && threadIdx.x == 32) p.clk[blockIdx.x * 16 + 12] = (long long)gtimer();
+  if (probe && threadIdx.x == 32) p.clk[blockIdx.x * 16 + 12] = (long long)gtimer();
+#undef P2P_CLK
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -519,23 +524,27 @@ extern "C" void p2p_debug_halo_clocks(void* buf) { g_halo_clk = static_cast<long
 template <int CIN_BLK>
 static int launch_halo_swap(const CUtensorMap& ma, const CUtensorMap& mb, const HaloParams& p, int grid, int smem,
                             cudaStream_t st) {
-  static int attr_smem = 0;
-  if (smem > attr_smem) {
-    P2P_CUDA(cudaFuncSetAttribute(conv_halo_swap_kernel<CIN_BLK>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attr_smem = smem;
+  trace_kernel("conv_halo_swap<%d> rows=%d taps=%d chunks=%d nb=%d blocks=%dx%d", CIN_BLK, p.rows, p.n_taps, p.c_chunks,
+               p.nb, p.blocks_h, p.blocks_w);
+  if (p.clk != nullptr) {           // tools/halo_clocks.py only
+    static SmemOptIn optin_probe;
+    P2P_CUDA(ensure_dyn_smem(conv_halo_swap_kernel<CIN_BLK, true>, optin_probe, smem));
+    conv_halo_swap_kernel<CIN_BLK, true><<<grid, 352, smem, st>>>(ma, mb, p);
+    P2P_LAUNCH_CHECK();
   }
-  conv_halo_swap_kernel<CIN_BLK><<<grid, 352, smem, st>>>(ma, mb, p);
+  static SmemOptIn optin;
+  P2P_CUDA(ensure_dyn_smem(conv_halo_swap_kernel<CIN_BLK, false>, optin, smem));
+  conv_halo_swap_kernel<CIN_BLK, false><<<grid, 352, smem, st>>>(ma, mb, p);
   P2P_LAUNCH_CHECK();
 }
 
 template <int BLOCK_N, int CIN_BLK>
 static int launch_halo(const CUtensorMap& ma, const CUtensorMap& mb, const HaloParams& p, int grid, int smem,
                        cudaStream_t st) {
-  static int attr_smem = 0;
-  if (smem > attr_smem) {
-    P2P_CUDA(cudaFuncSetAttribute(conv_halo_kernel<BLOCK_N, CIN_BLK>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attr_smem = smem;
-  }
+  static SmemOptIn optin;
+  P2P_CUDA(ensure_dyn_smem(conv_halo_kernel<BLOCK_N, CIN_BLK>, optin, smem));
+  trace_kernel("conv_halo<%d,%d> resident=%d taps=%d chunks=%d nb=%d", BLOCK_N, CIN_BLK, p.resident, p.n_taps, p.c_chunks,
+               p.nb);
   conv_halo_kernel<BLOCK_N, CIN_BLK><<<grid, 224, smem, st>>>(ma, mb, p);
   P2P_LAUNCH_CHECK();
 }

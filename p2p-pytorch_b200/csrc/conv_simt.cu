@@ -204,6 +204,7 @@ int conv_fwd_simt(const p2p_conv* c, const void* in, const void* w, const float*
   const ConvDims d = dims_of(c);
   const int64_t M = (int64_t)d.N * d.Ho * d.Wo;
   dim3 grid(cdiv(M, TM), cdiv(d.Co, TN));
+  trace_kernel("conv_simt fwd dtype=%d", dtype);
   P2P_DISPATCH(dtype, conv_simt_kernel<T, false><<<grid, 256, 0, st>>>((const T*)in, (const T*)w, bias, (T*)out, d););
   P2P_LAUNCH_CHECK();
 }
@@ -212,6 +213,7 @@ int conv_dgrad_simt(const p2p_conv* c, const void* dout, const void* wt, void* d
   const ConvDims d = dims_of(c);
   const int64_t M = (int64_t)d.N * d.Hi * d.Wi;
   dim3 grid(cdiv(M, TM), cdiv(d.Ci, TN));
+  trace_kernel("conv_simt dgrad dtype=%d", dtype);
   P2P_DISPATCH(dtype,
                conv_simt_kernel<T, true><<<grid, 256, 0, st>>>((const T*)dout, (const T*)wt, nullptr, (T*)din, d););
   P2P_LAUNCH_CHECK();
@@ -229,6 +231,7 @@ int conv_wgrad_simt(const p2p_conv* c, const void* in, const void* dout, float* 
   ppc = ((ppc + TK - 1) / TK) * TK;
   chunks = (int)((P + ppc - 1) / ppc);
   dim3 grid(gx, gy, chunks);
+  trace_kernel("conv_wgrad_simt dtype=%d", dtype);
   P2P_DISPATCH(dtype, conv_wgrad_simt_kernel<T><<<grid, 256, 0, st>>>((const T*)in, (const T*)dout, dw, d, ppc););
   P2P_LAUNCH_CHECK();
 }

@@ -185,12 +185,9 @@ template <int BLOCK_N, int CIN_BLK>
 static int launch_cfg(const CUtensorMap& ma, const CUtensorMap& mb, const TcConvParams& p, int grid_x, int grid_y,
                       cudaStream_t st) {
   using Cfg = TcCfg<BLOCK_N, CIN_BLK>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    P2P_CUDA(cudaFuncSetAttribute(conv_tc_kernel<BLOCK_N, CIN_BLK>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  Cfg::SMEM));
-    attr_set = true;
-  }
+  static SmemOptIn optin;
+  P2P_CUDA(ensure_dyn_smem(conv_tc_kernel<BLOCK_N, CIN_BLK>, optin, Cfg::SMEM));
+  trace_kernel("conv_tc<%d,%d> tw=%d stride=%d taps=%d chunks=%d", BLOCK_N, CIN_BLK, p.tw, p.in_mul, p.n_taps, p.c_chunks);
   conv_tc_kernel<BLOCK_N, CIN_BLK><<<dim3(grid_x, grid_y), 192, Cfg::SMEM, st>>>(ma, mb, p);
   P2P_LAUNCH_CHECK();
 }

@@ -311,11 +311,10 @@ int conv_wgrad_halo(const p2p_conv* c, const void* in, const void* dout, float* 
     if (int e = make_map_bf16(&my, dout, 4, dims, strides, box, es, p.co_blk * 2)) return e;
   }
   const int smem = stages * p.stage_bytes + 1024;
-  static int attr_smem = 0;
-  if (smem > attr_smem) {
-    P2P_CUDA(cudaFuncSetAttribute(conv_wgrad_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attr_smem = smem;
-  }
+  static SmemOptIn optin;
+  P2P_CUDA(ensure_dyn_smem(conv_wgrad_halo_kernel, optin, smem));
+  trace_kernel("conv_wgrad_halo cin_blk=%d chunks=%d ky_b=%d n_cols=%d mt=%d stages=%d", cin_blk, n_chunks, p.ky_b,
+               p.n_cols, p.mt, stages);
   conv_wgrad_halo_kernel<<<dim3(groups, n_tiles_n, splits), 192, smem, st>>>(mx, my, p);
   P2P_LAUNCH_CHECK();
 }

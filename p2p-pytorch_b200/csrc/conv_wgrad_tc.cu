@@ -271,11 +271,10 @@ int conv_wgrad_tc(const p2p_conv* c, const void* in, const void* dout, float* dw
     const uint32_t es[4] = {1, 1, 1, 1};
     if (int e = make_map_bf16(&my, dout, 4, dims, strides, box, es, co_blk * 2)) return e;
   }
-  static bool attr_set = false;
-  if (!attr_set) {
-    P2P_CUDA(cudaFuncSetAttribute(conv_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
-    attr_set = true;
-  }
+  static SmemOptIn optin;
+  P2P_CUDA(ensure_dyn_smem(conv_wgrad_tc_kernel, optin, 220 * 1024));
+  trace_kernel("conv_wgrad_tc cin_blk=%d n_cols=%d mt=%d pix=%d tw=%d stride=%d stages=%d", cin_blk, n_cols, mt, p.pix,
+               p.tw, c->stride, stages);
   conv_wgrad_tc_kernel<<<dim3(groups, n_tiles, splits), 192, smem, st>>>(mx, my, p);
   P2P_LAUNCH_CHECK();
 }

@@ -852,11 +852,50 @@ __global__ void __launch_bounds__(256) c_output_kernel(const T* __restrict__ res
   }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// 8-bit image batch -> the fp32 tensors the iteration consumes (dataset.py:19-20,30-40: ToTensor = x / 255,
+// Normalize(0.5, 0.5) = (t - 0.5) / 0.5), same fp32 operations in the same order as torchvision, and optionally
+// the 3-bit quantised generator input compress(b * 0.5 + 0.5, bits) (generate_dataset.py:29-34) in the same pass.
+// 16 pixels-channels per thread: one 16-byte load, four 16-byte stores per output.
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float decode_u8(uint32_t v) { return __fdiv_rn(__fdiv_rn((float)v, 255.f) - 0.5f, 0.5f); }
+__device__ __forceinline__ float quantise_unit(float real, float q) {
+  const float t = fminf(fmaxf(real * 0.5f + 0.5f, 0.f), 1.f) * q;
+  return __fdiv_rn(rintf(t), q);          // torch.round is round-half-to-even, like rintf
+}
+__global__ void __launch_bounds__(256) decode_u8_kernel(const uint8_t* __restrict__ src, float* __restrict__ dst,
+                                                        float* __restrict__ quant, int64_t n, float q) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x * 16;
+  for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 16; i < n; i += stride) {
+    if (i + 16 <= n) {
+      const uint4 u = *reinterpret_cast<const uint4*>(src + i);
+      const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        float4 f;
+        f.x = decode_u8(w[k] & 0xffu); f.y = decode_u8((w[k] >> 8) & 0xffu);
+        f.z = decode_u8((w[k] >> 16) & 0xffu); f.w = decode_u8(w[k] >> 24);
+        *reinterpret_cast<float4*>(dst + i + 4 * k) = f;
+        if (quant != nullptr)
+          *reinterpret_cast<float4*>(quant + i + 4 * k) =
+              make_float4(quantise_unit(f.x, q), quantise_unit(f.y, q), quantise_unit(f.z, q), quantise_unit(f.w, q));
+      }
+    } else {
+      for (int64_t j = i; j < n; ++j) {
+        const float f = decode_u8(src[j]);
+        dst[j] = f;
+        if (quant != nullptr) quant[j] = quantise_unit(f, q);
+      }
+    }
+  }
+}
+
 }  // namespace p2p
 
 using namespace p2p;
 
 extern "C" {
+
 
 int p2p_g_input_prep(const float* x, void* dst, int B, int H, int W, int dtype, void* stream) {
   P2P_REQUIRE(x && dst && B > 0 && H > 0 && W > 0, "null pointer or empty shape");
@@ -1080,6 +1119,17 @@ int p2p_nchw_to_nhwc(const float* in, void* out, int B, int H, int W, int C, int
   P2P_REQUIRE(in && out && c_real <= C && C % 8 == 0, "null pointer");
   P2P_DISPATCH(dtype, nchw_to_nhwc_kernel<T><<<ew_grid((int64_t)B * H * W * (C / 8)), 256, 0, as_stream(stream)>>>(
                           in, (T*)out, B, H, W, C, c_real););
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_decode_u8(const uint8_t* src, float* dst, float* quant, int64_t n, int bits, void* stream) {
+  P2P_REQUIRE(src && dst && n > 0 && bits >= 1 && bits <= 16, "bad arguments");
+  P2P_REQUIRE(((uintptr_t)src % 16 == 0) && ((uintptr_t)dst % 16 == 0) && ((uintptr_t)quant % 16 == 0),
+              "buffers must be 16-byte aligned");
+  int64_t blocks = (n / 16 + 255) / 256;
+  if (blocks < 1) blocks = 1;
+  if (blocks > kSMs * 8) blocks = kSMs * 8;
+  decode_u8_kernel<<<(int)blocks, 256, 0, as_stream(stream)>>>(src, dst, quant, n, (float)((1 << bits) - 1));
   P2P_LAUNCH_CHECK();
 }
 

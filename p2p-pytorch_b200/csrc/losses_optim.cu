@@ -145,7 +145,13 @@ __global__ void tv_bwd_add_kernel(const float* __restrict__ x, const float* __re
 __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                                                    float* __restrict__ v, int64_t n4, int64_t n, float b1, float b2,
                                                    float step_size, float inv_sqrt_bc2, float eps, float gs,
-                                                   const int* __restrict__ step_dev) {
+                                                   const int* __restrict__ step_dev,
+                                                   const float* __restrict__ hyper_dev) {
+  if (hyper_dev != nullptr) {
+    // learning rate and gradient scale live in device memory too: a scheduler may change them between replays
+    step_size = hyper_dev[0];
+    gs = hyper_dev[1];
+  }
   if (step_dev != nullptr) {
     // step count lives in device memory (the launch is replayed from a CUDA graph): same double-precision bias
     // corrections as the host path; step_size arrives holding lr
@@ -289,7 +295,7 @@ int p2p_adam_step(float* p, const float* g, float* m, float* v, int64_t n, float
   if (blocks < 1) blocks = 1;
   if (blocks > kSMs * 16) blocks = kSMs * 16;
   adam_kernel<<<(int)blocks, 256, 0, as_stream(stream)>>>(p, g, m, v, n4, n, beta1, beta2, step_size, inv_sqrt_bc2, eps,
-                                                         grad_scale, nullptr);
+                                                         grad_scale, nullptr, nullptr);
   P2P_LAUNCH_CHECK();
 }
 
@@ -304,7 +310,22 @@ int p2p_adam_step_dev(float* p, const float* g, float* m, float* v, int64_t n, f
   if (blocks < 1) blocks = 1;
   if (blocks > kSMs * 16) blocks = kSMs * 16;
   adam_kernel<<<(int)blocks, 256, 0, as_stream(stream)>>>(p, g, m, v, n4, n, beta1, beta2, lr, 1.f, eps, grad_scale,
-                                                         step_dev);
+                                                         step_dev, nullptr);
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_adam_step_graph(float* p, const float* g, float* m, float* v, int64_t n, float beta1, float beta2, float eps,
+                        const int* step_dev, const float* hyper_dev, void* stream) {
+  P2P_REQUIRE(p && g && m && v && n > 0 && step_dev && hyper_dev, "bad arguments");
+  P2P_REQUIRE(((uintptr_t)p % 16 == 0) && ((uintptr_t)g % 16 == 0) && ((uintptr_t)m % 16 == 0) &&
+                  ((uintptr_t)v % 16 == 0),
+              "buffers must be 16-byte aligned");
+  const int64_t n4 = n / 4;
+  int64_t blocks = (n4 + 255) / 256;
+  if (blocks < 1) blocks = 1;
+  if (blocks > kSMs * 16) blocks = kSMs * 16;
+  adam_kernel<<<(int)blocks, 256, 0, as_stream(stream)>>>(p, g, m, v, n4, n, beta1, beta2, 0.f, 1.f, eps, 1.f, step_dev,
+                                                         hyper_dev);
   P2P_LAUNCH_CHECK();
 }
 

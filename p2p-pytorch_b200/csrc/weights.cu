@@ -415,7 +415,6 @@ int p2p_spectral_norm(int n_layers, const float* const* w_host, float* const* u_
 static __device__ __align__(256) float g_sn_scratch[P2P_SN_STATIC_MAX_FLOATS];
 
 namespace p2p {
-constexpr int kMaxDevices = 64;
 static float* g_sn_scratch_addr[kMaxDevices] = {};
 static std::mutex g_sn_scratch_mutex;
 

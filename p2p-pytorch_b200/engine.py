@@ -452,6 +452,8 @@ class DiscriminatorFunction(torch.autograd.Function):
         layer_cfg, sn_bufs = aux["layer_cfg"], aux["sn_bufs"]
         dt, dev = _state["dtype"], a.device
         dc = L.dtype_code(dt)
+        # identity of the pair for the first-layer cache: same storage, not written to since
+        pair_id = (a.data_ptr(), a._version, None if b is None else b.data_ptr(), None if b is None else b._version)
         a = a.detach().contiguous().float()
         ca, cb = a.shape[1], 0
         if b is not None:
@@ -471,7 +473,11 @@ class DiscriminatorFunction(torch.autograd.Function):
         # reuse the input pyramid and the first layer's outputs of the first one: that layer has no spectral norm, so
         # its weights -- unlike the later layers' W / sigma -- are identical in both passes.
         cache = aux.get("first_layer_cache")
-        reuse = bool(cache) and cache.get("key") == (tuple(a.shape), cb, dt, _state["impl"]) and not layer_cfg[0][3]
+        nl0 = len(layer_cfg)
+        w0_id = tuple((params[2 * sc * nl0].data_ptr(), params[2 * sc * nl0]._version, params[2 * sc * nl0 + 1]._version)
+                      for sc in range(NUM_D))
+        cache_key = (tuple(a.shape), cb, dt, _state["impl"], pair_id, w0_id)
+        reuse = bool(cache) and cache.get("key") == cache_key and not layer_cfg[0][3]
         pyr_shapes = cache["pyr_shapes"] if reuse else None
         xs32 = None
         if not reuse:
@@ -511,7 +517,7 @@ class DiscriminatorFunction(torch.autograd.Function):
                 plan = ConvPlan(B, cur.shape[1], cur.shape[2], cur.shape[3], cin_real, cout, 4, stride, 2, act)
                 plan.wp, plan.wt, plan.w1x1 = packs[(sc, j)].wp, packs[(sc, j)].wt, packs[(sc, j)].w1x1
                 if reuse and j == 0:
-                    o = cache["l0"][i]
+                    o = cache["l0"][i].detach()        # an alias of its own: each Function owns its output objects
                 else:
                     o = _empty((B, plan.Ho, plan.Wo, plan.Co), dt, dev)
                     plan.fwd(cur, bias, o, None)
@@ -527,7 +533,7 @@ class DiscriminatorFunction(torch.autograd.Function):
         ctx.pyr_shapes = pyr_shapes
         if cache is not None and not reuse:
             cache.clear()
-            cache.update(key=(tuple(a.shape), cb, dt, _state["impl"]), pyr_shapes=pyr_shapes,
+            cache.update(key=cache_key, pyr_shapes=pyr_shapes,
                          inputs=[inputs[i * nl] for i in range(NUM_D)], l0=[outs[i * nl] for i in range(NUM_D)])
         return tuple(outs)
 

@@ -46,12 +46,15 @@ def save_checkpoint(path: str, epoch: int, net_g, net_c, **extra) -> None:
     torch.save(state, path)
 
 
-def load_checkpoint(path: str, net_g, net_c=None, net_d=None, map_location: Optional[str] = None) -> int:
+def load_checkpoint(path: str, net_g, net_c=None, net_d=None, map_location: Optional[str] = None,
+                    trusted: bool = False) -> int:
     """Load a file written by the reference (or by save_checkpoint) and return its `epoch` (train.py:103-118 reads
-    the same keys; entries the file does not hold are skipped)."""
+    the same keys; entries the file does not hold are skipped).  The format holds an int and tensor state_dicts
+    only, so the file is read with `weights_only=True`; pass `trusted=True` for a file of your own that carries
+    other pickled objects (unpickling runs arbitrary code)."""
     if not os.path.isfile(path):
         raise FileNotFoundError(path)
-    state = torch.load(path, map_location=map_location, weights_only=False)
+    state = torch.load(path, map_location=map_location, weights_only=not trusted)
     net_g.load_state_dict(state["state_dict_g"])
     if net_c is not None and "state_dict_c" in state:
         net_c.load_state_dict(state["state_dict_c"])

@@ -50,6 +50,8 @@ class FusedAdam(torch.optim.Optimizer):
                 p.grad = self.flat_g[off:off + k].view(p.shape)
         self._steps = 0
         self._step_t = None     # device-side step count (capturable mode)
+        self._hyper_t = None    # device-side [lr, grad_scale] (capturable mode) and the host values it holds
+        self._hyper_host = None
         self.grad_scale = 1.0   # set to 1/world_size by the data-parallel trainer (all-reduce is a sum)
 
     @property
@@ -67,6 +69,20 @@ class FusedAdam(torch.optim.Optimizer):
         host-dependent launch and can be recorded into, and replayed from, a CUDA graph."""
         if self._step_t is None:
             self._step_t = torch.full((1,), self._steps, dtype=torch.int32, device=self.flat_p.device)
+            self._hyper_t = torch.zeros(2, dtype=torch.float32, device=self.flat_p.device)
+            self.sync_hyper()
+
+    def sync_hyper(self):
+        """Capturable mode: bring the device copy of (lr, grad_scale) up to date with `param_groups[0]['lr']` and
+        `grad_scale` -- what torch.optim.lr_scheduler (networks.py:104-125, stepped at train.py:441-443) changes
+        between iterations.  A tiny host-to-device copy, issued only when a value changed; the owner of a captured
+        graph calls this before every replay (Pix2PixTrainer.step does)."""
+        if self._hyper_t is None:
+            return
+        cur = (float(self.param_groups[0]["lr"]), float(self.grad_scale))
+        if cur != self._hyper_host:
+            self._hyper_t.copy_(torch.tensor(cur, dtype=torch.float32), non_blocking=False)
+            self._hyper_host = cur
 
     def _rebind_grads(self):
         """Make sure every p.grad is still the flat view (a caller may have used set_to_none or assigned one)."""
@@ -94,10 +110,12 @@ class FusedAdam(torch.optim.Optimizer):
         self._rebind_grads()
         g = self.param_groups[0]
         if self._step_t is not None:
+            if not torch.cuda.is_current_stream_capturing():
+                self.sync_hyper()          # (inside a capture the recorded kernel only keeps the POINTER)
             self._step_t.add_(1)
-            call("p2p_adam_step_dev", ptr(self.flat_p), ptr(self.flat_g), ptr(self.exp_avg), ptr(self.exp_avg_sq),
-                 self.numel, float(g["lr"]), float(g["betas"][0]), float(g["betas"][1]), float(g["eps"]),
-                 ptr(self._step_t), float(self.grad_scale))
+            call("p2p_adam_step_graph", ptr(self.flat_p), ptr(self.flat_g), ptr(self.exp_avg), ptr(self.exp_avg_sq),
+                 self.numel, float(g["betas"][0]), float(g["betas"][1]), float(g["eps"]), ptr(self._step_t),
+                 ptr(self._hyper_t))
             return
         self._steps += 1
         call("p2p_adam_step", ptr(self.flat_p), ptr(self.flat_g), ptr(self.exp_avg), ptr(self.exp_avg_sq), self.numel,

@@ -81,6 +81,11 @@ class Pix2PixTrainer:
             self.optimizer_g.make_capturable()
             self.optimizer_d.make_capturable()
 
+    def _sync_hyper(self):
+        """learning rates changed by a scheduler since the last call reach the captured Adam launches (device memory)"""
+        self.optimizer_g.sync_hyper()
+        self.optimizer_d.sync_hyper()
+
     def broadcast_parameters(self, src: int = 0):
         """identical replicas at start (rank `src` wins), including BatchNorm buffers and SN u/v"""
         if self.world == 1:
@@ -95,33 +100,61 @@ class Pix2PixTrainer:
                 if not p.requires_grad:
                     dist.broadcast(p.data, src)
 
-    def step(self, real_a: torch.Tensor, real_b: torch.Tensor, g_input: torch.Tensor) -> Dict[str, torch.Tensor]:
+    def step(self, real_a: torch.Tensor, real_b: torch.Tensor, g_input: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
+        """One iteration (train.py:294-390, VGG term off).  Inputs, host (pinned) or device tensors:
+          * fp32 [B,3,H,W] in [-1,1] (what the reference's DataLoader yields, dataset.py:30-40) plus the generator
+            input `g_input` (train.py:297-300 feeds compress(net_c(real_b), 3); step_full() computes that);
+          * or uint8 [B,3,H,W] images: ToTensor + Normalize run on the device (p2p_decode_u8, bit-identical to
+            torchvision's fp32 arithmetic), a quarter of the host-to-device bytes; with g_input=None the generator
+            input is compress(real_b * 0.5 + 0.5, 3) (generate_dataset.py:29-34), made in the same pass."""
+        if real_a.dtype != real_b.dtype or real_a.dtype not in (torch.float32, torch.uint8):
+            raise ValueError("real_a / real_b must both be float32 or both be uint8")
+        if g_input is None and real_a.dtype != torch.uint8:
+            raise ValueError("float inputs need g_input (step_full() derives it with the compression network)")
+        args = (real_a, real_b) if g_input is None else (real_a, real_b, g_input)
         if not self.cuda_graph:
-            return self._step_eager(real_a, real_b, g_input)
-        key = (tuple(real_a.shape), tuple(real_b.shape), tuple(g_input.shape), E.get_precision())
+            return self._step_any(*[t.cuda(non_blocking=True) for t in args])
+        key = (tuple((tuple(t.shape), t.dtype) for t in args), E.get_precision())
         rec = self._graphs.get(key)
         if rec is None:
             if self._eager_calls < self.graph_warmup:
                 # lazily created workspaces, kernel attributes and NCCL communicators come to life here
                 self._eager_calls += 1
-                return self._step_eager(real_a.cuda(non_blocking=True), real_b.cuda(non_blocking=True),
-                                        g_input.cuda(non_blocking=True))
-            rec = self._capture(real_a, real_b, g_input)
+                return self._step_any(*[t.cuda(non_blocking=True) for t in args])
+            rec = self._capture(args)
             self._graphs[key] = rec
         pre = self._prefetched
-        if pre is not None and pre["ids"] == (id(real_a), id(real_b), id(g_input)):
+        if pre is not None and pre["ids"] == tuple(id(t) for t in args):
             # the batch was staged by prefetch(): its host->device copy ran beside the previous iteration
             torch.cuda.current_stream().wait_event(pre["event"])
             srcs = pre["staged"]
         else:
-            srcs = (real_a, real_b, g_input)
+            srcs = args
         self._prefetched = None
         for dst, src in zip(rec["inputs"], srcs):
             dst.copy_(src, non_blocking=True)
         if pre is not None and srcs is pre["staged"]:
             pre["free"].record(torch.cuda.current_stream())         # the staging slot may be overwritten from here on
+        self._sync_hyper()
         rec["graph"].replay()
         return rec["outputs"]
+
+    def _decode_u8(self, a8: torch.Tensor, b8: torch.Tensor, want_g_input: bool):
+        from . import _lib as L
+        a8, b8 = a8.contiguous(), b8.contiguous()
+        ra = torch.empty(a8.shape, dtype=torch.float32, device=a8.device)
+        rb = torch.empty(b8.shape, dtype=torch.float32, device=b8.device)
+        gi = torch.empty(b8.shape, dtype=torch.float32, device=b8.device) if want_g_input else None
+        L.call("p2p_decode_u8", L.ptr(a8), L.ptr(ra), None, a8.numel(), 3)
+        L.call("p2p_decode_u8", L.ptr(b8), L.ptr(rb), L.ptr(gi), b8.numel(), 3)
+        return ra, rb, gi
+
+    def _step_any(self, real_a, real_b, g_input=None):
+        """device tensors, fp32 or uint8 (see step())"""
+        if real_a.dtype == torch.uint8:
+            real_a, real_b, gi = self._decode_u8(real_a, real_b, g_input is None)
+            g_input = gi if g_input is None else g_input
+        return self._step_eager(real_a, real_b, g_input)
 
     def step_full(self, real_a: torch.Tensor, real_b: torch.Tensor, phase3: bool = True) -> Dict[str, torch.Tensor]:
         """The iteration as the reference executes it (train.py:294-402, VGG terms off): the generator input is
@@ -150,6 +183,7 @@ class Pix2PixTrainer:
             for dst, src in zip(inputs, (real_a, real_b)):
                 dst.copy_(src, non_blocking=True)
             graph = torch.cuda.CUDAGraph()
+            self._sync_hyper()
             torch.cuda.synchronize()
             before = L.launch_count()
             with torch.cuda.graph(graph):
@@ -158,6 +192,7 @@ class Pix2PixTrainer:
             rec = self._graphs[key] = {"graph": graph, "inputs": inputs, "outputs": outputs}
         for dst, src in zip(rec["inputs"], (real_a, real_b)):
             dst.copy_(src, non_blocking=True)
+        self._sync_hyper()
         rec["graph"].replay()
         return rec["outputs"]
 
@@ -175,11 +210,12 @@ class Pix2PixTrainer:
             out["loss_c"] = loss_c
         return out
 
-    def prefetch(self, real_a: torch.Tensor, real_b: torch.Tensor, g_input: torch.Tensor) -> None:
-        """Start copying the NEXT batch (pinned host tensors) to the device on a side stream while the current
-        iteration runs; the following step() called with the same three tensor objects picks the staged copy up
+    def prefetch(self, real_a: torch.Tensor, real_b: torch.Tensor, g_input: Optional[torch.Tensor] = None) -> None:
+        """Start copying the NEXT batch (pinned host tensors, fp32 or uint8) to the device on a side stream while the
+        current iteration runs; the following step() called with the same tensor objects picks the staged copy up
         (what a DataLoader's pin_memory + non_blocking pipeline does for the reference loop, train.py:296-298)."""
         dev = self.optimizer_g.flat_p.device
+        args = (real_a, real_b) if g_input is None else (real_a, real_b, g_input)
         if self._copy_stream is None:
             self._copy_stream = torch.cuda.Stream(device=dev)
             self._staging = [None, None]
@@ -187,29 +223,30 @@ class Pix2PixTrainer:
             for ev in self._slot_free:
                 ev.record(torch.cuda.current_stream())
         slot = self._stage_slot = 1 - getattr(self, "_stage_slot", 1)
-        shapes = tuple(tuple(t.shape) for t in (real_a, real_b, g_input))
-        if self._staging[slot] is None or tuple(tuple(t.shape) for t in self._staging[slot]) != shapes:
-            self._staging[slot] = [torch.empty(s, dtype=torch.float32, device=dev) for s in shapes]
+        sig = tuple((tuple(t.shape), t.dtype) for t in args)
+        if self._staging[slot] is None or tuple((tuple(t.shape), t.dtype) for t in self._staging[slot]) != sig:
+            self._staging[slot] = [torch.empty(sh, dtype=dt, device=dev) for sh, dt in sig]
         self._copy_stream.wait_event(self._slot_free[slot])            # the slot's previous reader is done with it
         with torch.cuda.stream(self._copy_stream):
-            for dst, src in zip(self._staging[slot], (real_a, real_b, g_input)):
+            for dst, src in zip(self._staging[slot], args):
                 dst.copy_(src, non_blocking=True)
             ev = torch.cuda.Event()
             ev.record(self._copy_stream)
-        self._prefetched = {"ids": (id(real_a), id(real_b), id(g_input)), "staged": self._staging[slot], "event": ev,
+        self._prefetched = {"ids": tuple(id(t) for t in args), "staged": self._staging[slot], "event": ev,
                             "free": self._slot_free[slot]}
 
-    def _capture(self, real_a, real_b, g_input):
+    def _capture(self, args):
         from . import _lib as L
         dev = self.optimizer_g.flat_p.device
-        inputs = [torch.empty(t.shape, dtype=torch.float32, device=dev) for t in (real_a, real_b, g_input)]
-        for dst, src in zip(inputs, (real_a, real_b, g_input)):
+        inputs = [torch.empty(t.shape, dtype=t.dtype, device=dev) for t in args]
+        for dst, src in zip(inputs, args):
             dst.copy_(src, non_blocking=True)
         graph = torch.cuda.CUDAGraph()
+        self._sync_hyper()
         torch.cuda.synchronize()
         before = L.launch_count()
         with torch.cuda.graph(graph):
-            outputs = self._step_eager(*inputs)
+            outputs = self._step_any(*inputs)
         self.graph_launches = L.launch_count() - before
         return {"graph": graph, "inputs": inputs, "outputs": outputs}
 

@@ -120,3 +120,92 @@ def test_prefetch_stages_the_next_batch():
         losses[use_prefetch] = rec
     for (d0, g0), (d1, g1) in zip(losses[False], losses[True]):
         assert abs(d0 - d1) <= 1e-3 * abs(d0) and abs(g0 - g1) <= 1e-3 * abs(g0)
+
+
+def test_lr_scheduler_reaches_the_captured_adam_step():
+    """The reference steps its LR schedulers every epoch (train.py:441-443; get_scheduler, networks.py:104-109 builds a
+    LambdaLR).  Under cuda_graph=True the Adam launches are replayed, so lr must not be frozen at capture time: after
+    the scheduler halves it, a replayed step moves the weights half as far, exactly like the eager trainer."""
+    import p2p_pytorch_b200 as P
+    P.set_precision("fp32")
+    batches = [tuple(t.to(DEV) for t in orc.synthetic_batch(2, 32, 32, 90 + i)) for i in range(6)]
+    deltas = {}
+    for graph in (False, True):
+        g, d = _nets(P)
+        tr = P.Pix2PixTrainer(g, d, cuda_graph=graph, graph_warmup=1)
+        scheds = [torch.optim.lr_scheduler.LambdaLR(o, lr_lambda=lambda e: 0.5 ** e)
+                  for o in (tr.optimizer_g, tr.optimizer_d)]
+        rec = []
+        for i, bt in enumerate(batches):
+            before = (tr.optimizer_g.flat_p.clone(), tr.optimizer_d.flat_p.clone())
+            tr.step(*bt)
+            rec.append(tuple((o.flat_p - b).abs().mean().item() for o, b in zip((tr.optimizer_g, tr.optimizer_d), before)))
+            if i == 2:                      # "end of epoch": captured after step 1 (graph_warmup=1), so this is post-capture
+                for s in scheds:
+                    s.step()
+                assert abs(tr.optimizer_g.param_groups[0]["lr"] - 1e-4) < 1e-12
+        deltas[graph] = rec
+        if graph:
+            assert len(tr._graphs) == 1
+    for graph in (False, True):
+        for net in (0, 1):
+            # Adam's per-step movement is ~lr while m / sqrt(v) stays of order one: halving lr halves it
+            ratio = deltas[graph][3][net] / deltas[graph][2][net]
+            assert 0.35 <= ratio <= 0.65, (graph, net, ratio, deltas[graph])
+    for i in range(len(batches)):
+        for net in (0, 1):
+            assert abs(deltas[True][i][net] - deltas[False][i][net]) <= 0.05 * deltas[False][i][net], (i, net, deltas)
+
+
+def test_adam_graph_entry_reads_lr_and_scale_from_device():
+    from p2p_pytorch_b200._lib import call, ptr
+    gen = torch.Generator(device=DEV).manual_seed(6)
+    n = 50_000
+    p0 = torch.randn(n, device=DEV, generator=gen)
+    state = [[p0.clone(), torch.zeros(n, device=DEV), torch.zeros(n, device=DEV)] for _ in range(2)]
+    step_t = torch.zeros(1, dtype=torch.int32, device=DEV)
+    hyper = torch.zeros(2, device=DEV)
+    for step in range(1, 6):
+        lr, gs = 2e-4 * 0.7 ** step, 1.0 / step
+        grad = torch.randn(n, device=DEV, generator=gen)
+        p, m, v = state[0]
+        call("p2p_adam_step", ptr(p), ptr(grad), ptr(m), ptr(v), n, lr, 0.5, 0.999, 1e-8, step, gs)
+        p, m, v = state[1]
+        step_t.add_(1)
+        hyper.copy_(torch.tensor([lr, gs]))
+        call("p2p_adam_step_graph", ptr(p), ptr(grad), ptr(m), ptr(v), n, 0.5, 0.999, 1e-8, ptr(step_t), ptr(hyper))
+    for x, y in zip(*state):
+        assert torch.allclose(x, y, rtol=1e-6, atol=1e-9)
+
+
+@pytest.mark.parametrize("graph", [False, True], ids=["eager", "graph"])
+def test_uint8_batches_equal_float_batches(graph):
+    """step(uint8 a, uint8 b) == step(ToTensor+Normalize(a), ..(b), compress(b*0.5+0.5, 3)): the device-side decode
+    is bit-identical to the reference's input pipeline, so the two iterations agree to the run-to-run noise of the
+    split-K atomics (fp32 mode).  Also through prefetch() with pinned uint8 tensors."""
+    import p2p_pytorch_b200 as P
+    P.set_precision("fp32")
+    gen = torch.Generator().manual_seed(11)
+    rec = {}
+    for mode in ("float", "u8"):
+        g, d = _nets(P)
+        tr = P.Pix2PixTrainer(g, d, cuda_graph=graph, graph_warmup=1)
+        losses = []
+        gen.manual_seed(11)
+        batches = [(torch.randint(0, 256, (2, 3, 32, 32), generator=gen, dtype=torch.uint8),
+                    torch.randint(0, 256, (2, 3, 32, 32), generator=gen, dtype=torch.uint8)) for _ in range(4)]
+        if mode == "u8":
+            batches = [tuple(t.pin_memory() for t in bt) for bt in batches]
+        for i, (a8, b8) in enumerate(batches):
+            if mode == "float":
+                fa, fb = (t.float().div(255).sub_(0.5).div_(0.5) for t in (a8, b8))
+                out = tr.step(fa.to(DEV), fb.to(DEV), orc.compress(fb * 0.5 + 0.5, 3).to(DEV))
+            else:
+                out = tr.step(a8, b8)
+                if graph and i + 1 < len(batches):
+                    tr.prefetch(*batches[i + 1])
+            losses.append((out["loss_d"].item(), out["loss_g"].item(), out["fake_b"].float().abs().sum().item()))
+        rec[mode] = losses
+    for x, y in zip(rec["float"], rec["u8"]):
+        for u, v in zip(x, y):
+            assert abs(u - v) <= 1e-3 * abs(u), (rec["float"], rec["u8"])

@@ -396,3 +396,23 @@ def test_fat_column_conv_matches_conv2d(shape):
     assert relerr(from_stored(din, cin), xr.grad) <= 1e-2
     if Ci > cin:
         assert din[..., cin:].abs().max().item() == 0
+
+
+def test_decode_u8_is_bit_identical_to_totensor_normalize():
+    """p2p_decode_u8 against the reference's input pipeline (dataset.py:19-20,30-40: ToTensor, Normalize(0.5, 0.5))
+    and its quantiser (generate_dataset.py:29-34), all 256 byte values and a ragged length."""
+    from oracle import pix2pix_oracle as orc
+    g = torch.Generator().manual_seed(3)
+    u8 = torch.cat([torch.arange(256, dtype=torch.uint8), torch.randint(0, 256, (3 * 37 * 41 + 5,), generator=g, dtype=torch.uint8)])
+    t = u8.float().div(255)                       # ToTensor
+    ref = t.clone().sub_(0.5).div_(0.5)           # Normalize (torchvision: tensor.sub_(mean).div_(std))
+    ref_q = orc.compress(ref * 0.5 + 0.5, 3)
+    src = u8.to(DEV)
+    dst = torch.empty(u8.numel(), device=DEV)
+    q = torch.empty(u8.numel(), device=DEV)
+    L.call("p2p_decode_u8", src.data_ptr(), dst.data_ptr(), q.data_ptr(), u8.numel(), 3)
+    assert torch.equal(dst.cpu(), ref)
+    assert torch.equal(q.cpu(), ref_q)
+    dst2 = torch.empty(u8.numel(), device=DEV)
+    L.call("p2p_decode_u8", src.data_ptr(), dst2.data_ptr(), None, u8.numel(), 3)
+    assert torch.equal(dst2, dst)
