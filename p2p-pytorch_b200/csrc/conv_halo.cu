@@ -35,7 +35,6 @@ struct HaloParams {
   int rows;                             // output rows per block: 32, or 16..32 (even) in the swapped kernel
   int a_bytes;                          // bytes of one halo chunk buffer (1024-aligned)
   int nb;                               // weight ring depth (streaming) / number of resident tiles
-  int pieces, na;                       // swapped kernel: pixel blocks per pass (1..3), halo slots (2..4)
   int resident;                         // 1: all n_taps * c_chunks weight tiles stay in shared memory
   EpiOut epi;                           // output addressing, bias handled separately
   int64_t out_sN;
@@ -262,31 +261,19 @@ __global__ void __launch_bounds__(224, 1)
 // ---------------------------------------------------------------------------------------------------
 // PROBE = true compiles in the clock64 / %globaltimer stamps read by tools/halo_clocks.py (a separate instantiation:
 // the production kernel contains none of it).
-//
-// Pieces per pass (p.pieces = P).  A CTA's ingest from L2 is what bounds the streamed-weight layers: one 16 KB weight
-// tile per N = 256 MMA quadruple is 32 B/cycle per SM, and 148 SMs x (32 + 9.5 B/cycle of halo) is the ~6.3 KB/cycle the
-// L2 delivers (profiles/r01d_ncu_res_fwd.md).  With P > 1 a pass holds P pixel blocks ("pieces") at once -- P halos in
-// shared memory, P accumulators side by side in TMEM (P * 8 * rows <= 512 columns) -- and every weight tile that
-// arrives feeds P MMAs, so the weight bytes per FLOP drop by P.  The price: the accumulators fill all of TMEM, so the
-// epilogue of a pass no longer overlaps the MMAs of the next one (P = 1 keeps the two-set overlap).
-constexpr int kSwapEpiWarps = 16;                       // 4 groups x 4 TMEM lane quarters
-constexpr int kSwapThreads = (3 + kSwapEpiWarps) * 32;   // + halo producer, MMA issuer, weight producer
-
 template <int CIN_BLK, bool PROBE>
-__global__ void __launch_bounds__(kSwapThreads, 1)
+__global__ void __launch_bounds__(352, 1)
     conv_halo_swap_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                           const __grid_constant__ HaloParams p) {
   constexpr int RB = CIN_BLK * 2;
   constexpr int W_BYTES = 128 * RB;               // one [128 output channels x CIN_BLK] weight tile
-  constexpr int NA_MAX = 4;
-  constexpr uint32_t TMEM_COLS = 512;             // P = 1: two accumulator sets of 256 pixel columns; P > 1: one set
+  constexpr int NA = 2;
+  constexpr uint32_t TMEM_COLS = 512;             // two accumulator sets of 256 pixel columns
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  const int P = p.pieces, NA = p.na;
-  const int slot_bytes = P * p.a_bytes;           // one halo slot: the P pieces' halos of one channel chunk
-  uint8_t* sA = smem;                             // halo slots
-  uint8_t* sB = sA + NA * slot_bytes;             // weight ring
-  __shared__ uint64_t a_full[NA_MAX], a_empty[NA_MAX], b_full[8], b_empty[8], t_full[2], t_empty[2];
+  uint8_t* sA = smem;                             // halo chunks
+  uint8_t* sB = sA + NA * p.a_bytes;              // weight ring
+  __shared__ uint64_t a_full[NA], a_empty[NA], b_full[8], b_empty[8], t_full[2], t_empty[2];
   __shared__ uint32_t tmem_base_s;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -295,17 +282,14 @@ __global__ void __launch_bounds__(kSwapThreads, 1)
   if (probe && threadIdx.x == 0) p.clk[blockIdx.x * 16 + 8] = (long long)gtimer();
   const int blocks_per_img = p.blocks_w * p.blocks_h;
   const int items_per_ntile = blocks_per_img * p.n_img;
-  const int passes_per_ntile = (items_per_ntile + P - 1) / P;
-  const int n_passes = passes_per_ntile * p.n_tiles;
-  const int n_sets = P == 1 ? 2 : 1;
-  const uint32_t piece_cols = P == 1 ? 256u : (uint32_t)(8 * p.rows);
+  const int n_items = items_per_ntile * p.n_tiles;
 
   if (threadIdx.x == 0) {
     prefetch_tmap(&map_a);
     prefetch_tmap(&map_b);
     for (int s = 0; s < NA; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); }
     for (int s = 0; s < p.nb; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(&t_full[s], 1); mbar_init(&t_empty[s], kSwapEpiWarps); }
+    for (int s = 0; s < 2; ++s) { mbar_init(&t_full[s], 1); mbar_init(&t_empty[s], 8); }
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(&tmem_base_s, TMEM_COLS);
@@ -315,35 +299,30 @@ __global__ void __launch_bounds__(kSwapThreads, 1)
   const uint32_t tmem_base = tmem_base_s;
 
   if (warp == 0) {
-    // ===== halo producer: per (pass, chunk) one slot = one box per piece =====
+    // ===== halo producer =====
     if (elect_one()) {
       int ab = 0;
       uint32_t aph = 0;
-      for (int ps = blockIdx.x; ps < n_passes; ps += gridDim.x) {
-        const int q = ps % passes_per_ntile;
-        const int n_valid = min(P, items_per_ntile - q * P);
+      for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+        const int r = it % items_per_ntile;
+        const int img = r / blocks_per_img, br = r % blocks_per_img;
+        const int oy0 = (br / p.blocks_w) * p.rows, ox0 = (br % p.blocks_w) * 8;
         for (int c = 0; c < p.c_chunks; ++c) {
           mbar_wait(&a_empty[ab], aph ^ 1);
-          mbar_arrive_expect_tx(&a_full[ab], (uint32_t)(n_valid * p.HH * p.HW * RB));
-          for (int j = 0; j < n_valid; ++j) {
-            const int r = q * P + j;
-            const int img = r / blocks_per_img, br = r % blocks_per_img;
-            const int oy0 = (br / p.blocks_w) * p.rows, ox0 = (br % p.blocks_w) * 8;
-            tma_load_4d(sA + ab * slot_bytes + j * p.a_bytes, &map_a, &a_full[ab], c * CIN_BLK, ox0 + p.min_dw,
-                        oy0 + p.min_dh, img);
-          }
+          mbar_arrive_expect_tx(&a_full[ab], (uint32_t)(p.HH * p.HW * RB));
+          tma_load_4d(sA + ab * p.a_bytes, &map_a, &a_full[ab], c * CIN_BLK, ox0 + p.min_dw, oy0 + p.min_dh, img);
           if (++ab == NA) { ab = 0; aph ^= 1; }
         }
       }
     }
     __syncwarp();
-  } else if (warp == 2) {
+  } else if (warp == 10) {
     // ===== weight producer =====
     if (elect_one()) {
       int bs = 0;
       uint32_t bph = 0;
-      for (int ps = blockIdx.x; ps < n_passes; ps += gridDim.x) {
-        const int n0 = (ps / passes_per_ntile) * 128;
+      for (int it = blockIdx.x; it < n_items; it += gridDim.x) {
+        const int n0 = (it / items_per_ntile) * 128;
         for (int c = 0; c < p.c_chunks; ++c)
           for (int t = 0; t < p.n_taps; ++t) {
             mbar_wait(&b_empty[bs], bph ^ 1);
@@ -359,19 +338,15 @@ __global__ void __launch_bounds__(kSwapThreads, 1)
     const uint32_t idesc = umma_idesc_bf16(128, 8 * p.rows, 0, 0);   // N = pixels of one block (multiple of 16)
     const uint32_t x_hi = desc_hi((uint32_t)(p.HW * RB), RB);     // pixel row groups are HW halo rows apart
     const uint32_t w_hi = desc_hi(8 * RB, RB);
-    const uint32_t piece_step = (uint32_t)p.a_bytes >> 4;         // descriptor-address step between the pieces of a slot
     int ab = 0, bs = 0, li = 0;
     uint32_t aph = 0, bph = 0;
     const long long c_tot = P2P_CLK();
     long long c_te = 0, c_af = 0, c_t0;
     if (probe && lane == 0) p.clk[blockIdx.x * 16 + 9] = (long long)gtimer();
-    for (int ps = blockIdx.x; ps < n_passes; ps += gridDim.x, ++li) {
-      const int set = n_sets == 2 ? (li & 1) : 0;
-      const uint32_t tph = n_sets == 2 ? ((li >> 1) & 1) : (li & 1);
-      const int q = ps % passes_per_ntile;
-      const int n_valid = min(P, items_per_ntile - q * P);
+    for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++li) {
+      const int set = li & 1;
       c_t0 = P2P_CLK();
-      mbar_wait(&t_empty[set], tph ^ 1);
+      mbar_wait(&t_empty[set], ((li >> 1) & 1) ^ 1);
       c_te += P2P_CLK() - c_t0;
       tc_fence_after();
       const uint32_t acc = tmem_base + set * 256;
@@ -381,7 +356,7 @@ __global__ void __launch_bounds__(kSwapThreads, 1)
         mbar_wait(&a_full[ab], aph);
         c_af += P2P_CLK() - c_t0;
         tc_fence_after();
-        const uint32_t x_lo0 = desc_lo(smem_u32(sA + ab * slot_bytes), 16);
+        const uint32_t x_lo0 = desc_lo(smem_u32(sA + ab * p.a_bytes), 16);
         if (elect_one()) {
           int bs_l = bs;
           uint32_t bph_l = bph;
@@ -394,15 +369,8 @@ __global__ void __launch_bounds__(kSwapThreads, 1)
             const uint32_t w_lo = desc_lo(smem_u32(sB + bs_l * W_BYTES), 16);
             const uint32_t x_lo = x_lo0 + (uint32_t)p.taps[t].row_off16;
 #pragma unroll
-            for (int k = 0; k < CIN_BLK / 16; ++k) {
+            for (int k = 0; k < CIN_BLK / 16; ++k)
               umma_bf16_split(acc, w_lo + 2 * k, w_hi, x_lo + 2 * k, x_hi, idesc, first | (uint32_t)(t | k));
-              if (n_valid > 1)
-                umma_bf16_split(acc + piece_cols, w_lo + 2 * k, w_hi, x_lo + piece_step + 2 * k, x_hi, idesc,
-                                first | (uint32_t)(t | k));
-              if (n_valid > 2)
-                umma_bf16_split(acc + 2 * piece_cols, w_lo + 2 * k, w_hi, x_lo + 2 * piece_step + 2 * k, x_hi, idesc,
-                                first | (uint32_t)(t | k));
-            }
             umma_commit(&b_empty[bs_l]);
             if (++bs_l == p.nb) { bs_l = 0; bph_l ^= 1; }
           }
@@ -426,12 +394,11 @@ __global__ void __launch_bounds__(kSwapThreads, 1)
       p.clk[blockIdx.x * 16 + 2] = c_af;
       p.clk[blockIdx.x * 16 + 10] = (long long)gtimer();
     }
-  } else if (warp >= 3) {
-    // ===== epilogue (16 warps = 4 groups x 4 lane quarters): this thread owns output channel n0 + ch; the pass's
-    // accumulator columns are dealt out to the groups in units of 32 columns (= 4 block rows of 8 pixels) =====
-    const int q4 = warp & 3;                    // TMEM lane quarter this warp may read
-    const int grp = (warp - 3) >> 2;
-    const int ch = q4 * 32 + lane;
+  } else if (warp >= 2 && warp <= 9) {
+    // ===== epilogue (8 warps): this thread owns output channel n0 + ch for one half (16 rows) of the block =====
+    const int q = warp & 3;                     // TMEM lane quarter this warp may read
+    const int half = (warp - 2) >> 2;           // columns [128 * half, 128 * half + 128) = block rows 16*half ..
+    const int ch = q * 32 + lane;
     const bool lrelu = p.epi.act == P2P_ACT_LRELU;
     const bool even = (lane & 1) == 0;
     // lane pairs trade halves so that every lane owns one pixel x two channels: odd lanes first swap their own
@@ -439,18 +406,19 @@ __global__ void __launch_bounds__(kSwapThreads, 1)
     const uint32_t sel_own = even ? 0x3210u : 0x1032u;
     const uint32_t sel_word = even ? 0x7610u : 0x1076u;
     const int64_t sx = (int64_t)p.epi.w_mul * p.epi.out_sW;      // elements between horizontally adjacent pixels
-    const int ncols = 8 * p.rows;
-    const int upp = (ncols + 31) >> 5;          // 32-column units per piece (the last one may be half full)
     int li = 0, cur_n0 = -1;
     float bias = 0.f;
     bool real = false;
     double d_s = 0.0, d_ss = 0.0;
-    for (int ps = blockIdx.x; ps < n_passes; ps += gridDim.x, ++li) {
-      const int set = n_sets == 2 ? (li & 1) : 0;
-      const uint32_t tph = n_sets == 2 ? ((li >> 1) & 1) : (li & 1);
-      const int n0 = (ps / passes_per_ntile) * 128;
-      const int q = ps % passes_per_ntile;
-      const int n_valid = min(P, items_per_ntile - q * P);
+    for (int it = blockIdx.x; it < n_items; it += gridDim.x, ++li) {
+      const int set = li & 1;
+      const int n0 = (it / items_per_ntile) * 128;
+      const int r = it % items_per_ntile;
+      const int img = r / blocks_per_img, br = r % blocks_per_img;
+      const int oyb = (br / p.blocks_w) * p.rows;
+      const int oy0 = oyb + half * 16, ox0 = (br % p.blocks_w) * 8;
+      const int h_lim = min(p.epi.Hv, oyb + p.rows);            // rows of this block that exist
+      const int n_cols = 8 * min(16, p.rows - half * 16);       // accumulator columns of this half (>= 0)
       if (n0 != cur_n0) {
         if (cur_n0 >= 0 && real && p.epi.stats != nullptr) {
           atomicAdd(p.epi.stats + cur_n0 + ch, d_s);
@@ -461,44 +429,40 @@ __global__ void __launch_bounds__(kSwapThreads, 1)
         bias = (p.bias != nullptr && real) ? p.bias[n0 + ch] : 0.f;
         cur_n0 = n0;
       }
-      mbar_wait(&t_full[set], tph);
+      // the even lane stores channels (ch, ch+1) of the even pixel of a pair, the odd lane (ch-1, ch) of the odd one
+      __nv_bfloat16* obase = p.epi.out + (int64_t)img * p.out_sN + n0 + (even ? ch : ch - 1) +
+                             (int64_t)(ox0 * p.epi.w_mul + p.epi.w_off) * p.epi.out_sW + (even ? 0 : sx);
+      const bool all_real_x = __all_sync(0xffffffffu, real && ox0 + 8 <= p.epi.Wv);
+      const long long c_e0 = P2P_CLK();
+      mbar_wait(&t_full[set], (li >> 1) & 1);
+      const long long c_e1 = P2P_CLK();
       tc_fence_after();
       float s = 0.f, ss = 0.f;
-      const int n_units = n_valid * upp;
-      if (grp >= n_units) {                      // nothing to read for this group in this pass
+      if (n_cols <= 0) {                         // blocks of 16 rows: the upper half has nothing to read
         __syncwarp();
         if (lane == 0) mbar_arrive(&t_empty[set]);
       }
 #pragma unroll 1
-      for (int u = grp; u < n_units; u += 4) {
-        const int j = u / upp, j0 = (u - j * upp) << 5;
-        const int r = q * P + j;
-        const int img = r / blocks_per_img, br = r % blocks_per_img;
-        const int oyb = (br / p.blocks_w) * p.rows, ox0 = (br % p.blocks_w) * 8;
-        const int h_lim = min(p.epi.Hv, oyb + p.rows);            // rows of this block that exist
-        // the even lane stores channels (ch, ch+1) of the even pixel of a pair, the odd lane (ch-1, ch) of the odd one
-        __nv_bfloat16* obase = p.epi.out + (int64_t)img * p.out_sN + n0 + (even ? ch : ch - 1) +
-                               (int64_t)(ox0 * p.epi.w_mul + p.epi.w_off) * p.epi.out_sW + (even ? 0 : sx);
-        const bool all_real_x = __all_sync(0xffffffffu, real && ox0 + 8 <= p.epi.Wv);
+      for (int j0 = 0; j0 < n_cols; j0 += 32) {
         uint32_t v[32];
-        tmem_ld32(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(set * 256) + (uint32_t)j * piece_cols + (uint32_t)j0, v);
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(set * 256 + half * 128 + j0), v);
         tmem_ld_wait();
-        if (u + 4 >= n_units) {                  // this warp's last read of the accumulator set: hand it back
+        if (j0 + 32 >= n_cols) {                // last read of this accumulator set: hand it back to the MMA warp
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(&t_empty[set]);
         }
-        const int yy0 = oyb + (j0 >> 3);          // the 32 columns are 4 block rows of 8 pixels
+        const int yy0 = oy0 + (j0 >> 3);        // the 32 columns are 4 block rows of 8 pixels
         if (all_real_x && yy0 + 4 <= h_lim) {
 #pragma unroll
           for (int rr = 0; rr < 4; ++rr) {
             __nv_bfloat16* orow = obase + (int64_t)((yy0 + rr) * p.epi.h_mul + p.epi.h_off) * p.epi.out_sH;
 #pragma unroll
             for (int x = 0; x < 8; x += 2) {
-              const int jj = rr * 8 + x;
-              float f0 = __uint_as_float(v[jj]) + bias, f1 = __uint_as_float(v[jj + 1]) + bias;
+              const int j = rr * 8 + x;
+              float f0 = __uint_as_float(v[j]) + bias, f1 = __uint_as_float(v[j + 1]) + bias;
               if (lrelu) { f0 = fmaxf(f0, 0.2f * f0); f1 = fmaxf(f1, 0.2f * f1); }
-              const uint32_t pk = pack_bf16x2(f0, f1);    // (pixel jj, pixel jj+1) of my channel, rounded as stored
+              const uint32_t pk = pack_bf16x2(f0, f1);    // (pixel j, pixel j+1) of my channel, rounded as stored
               const float r0 = __uint_as_float(pk << 16), r1 = __uint_as_float(pk & 0xffff0000u);
               s += r0 + r1;
               ss = fmaf(r0, r0, fmaf(r1, r1, ss));
@@ -509,11 +473,11 @@ __global__ void __launch_bounds__(kSwapThreads, 1)
           }
         } else {
 #pragma unroll
-          for (int jj = 0; jj < 32; jj += 2) {
-            const int yy = yy0 + (jj >> 3), x = jj & 7;
+          for (int j = 0; j < 32; j += 2) {
+            const int yy = yy0 + (j >> 3), x = j & 7;
             const bool row_ok = yy < h_lim;
             const bool ok0 = row_ok && ox0 + x < p.epi.Wv, ok1 = row_ok && ox0 + x + 1 < p.epi.Wv;
-            float f0 = __uint_as_float(v[jj]) + bias, f1 = __uint_as_float(v[jj + 1]) + bias;
+            float f0 = __uint_as_float(v[j]) + bias, f1 = __uint_as_float(v[j + 1]) + bias;
             if (lrelu) { f0 = fmaxf(f0, 0.2f * f0); f1 = fmaxf(f1, 0.2f * f1); }
             if (!real || !ok0) f0 = 0.f;        // channel padding and positions outside the map are exact zeros
             if (!real || !ok1) f1 = 0.f;
@@ -531,6 +495,11 @@ __global__ void __launch_bounds__(kSwapThreads, 1)
       }
       d_s += (double)s;
       d_ss += (double)ss;
+      if (probe && threadIdx.x == 64) {
+        p.clk[blockIdx.x * 16 + 5] += c_e1 - c_e0;
+        p.clk[blockIdx.x * 16 + 6] += P2P_CLK() - c_e1;
+        p.clk[blockIdx.x * 16 + 11] = (long long)gtimer();
+      }
     }
     if (cur_n0 >= 0 && real && p.epi.stats != nullptr) {
       atomicAdd(p.epi.stats + cur_n0 + ch, d_s);
@@ -555,17 +524,17 @@ extern "C" void p2p_debug_halo_clocks(void* buf) { g_halo_clk = static_cast<long
 template <int CIN_BLK>
 static int launch_halo_swap(const CUtensorMap& ma, const CUtensorMap& mb, const HaloParams& p, int grid, int smem,
                             cudaStream_t st) {
-  trace_kernel("conv_halo_swap<%d> rows=%d pieces=%d taps=%d chunks=%d nb=%d blocks=%dx%d", CIN_BLK, p.rows, p.pieces,
-               p.n_taps, p.c_chunks, p.nb, p.blocks_h, p.blocks_w);
+  trace_kernel("conv_halo_swap<%d> rows=%d taps=%d chunks=%d nb=%d blocks=%dx%d", CIN_BLK, p.rows, p.n_taps, p.c_chunks,
+               p.nb, p.blocks_h, p.blocks_w);
   if (p.clk != nullptr) {           // tools/halo_clocks.py only
     static SmemOptIn optin_probe;
     P2P_CUDA(ensure_dyn_smem(conv_halo_swap_kernel<CIN_BLK, true>, optin_probe, smem));
-    conv_halo_swap_kernel<CIN_BLK, true><<<grid, kSwapThreads, smem, st>>>(ma, mb, p);
+    conv_halo_swap_kernel<CIN_BLK, true><<<grid, 352, smem, st>>>(ma, mb, p);
     P2P_LAUNCH_CHECK();
   }
   static SmemOptIn optin;
   P2P_CUDA(ensure_dyn_smem(conv_halo_swap_kernel<CIN_BLK, false>, optin, smem));
-  conv_halo_swap_kernel<CIN_BLK, false><<<grid, kSwapThreads, smem, st>>>(ma, mb, p);
+  conv_halo_swap_kernel<CIN_BLK, false><<<grid, 352, smem, st>>>(ma, mb, p);
   P2P_LAUNCH_CHECK();
 }
 
@@ -641,41 +610,10 @@ int run_halo_problem(const void* a_src, int N, int Hs, int Ws, int Ck, const voi
     if (blocks * 8 * p.rows > 2 * (int64_t)N * Hv * Wv) return -2;   // small maps: too many padded pixels per block
   }
   int ring_budget = budget;
-  p.pieces = 1;
-  p.na = 2;
   if (swap) {
     p.HH = p.rows + (mx_h - mn_h);
     p.a_bytes = ((p.HH * p.HW * rb + 1023) / 1024) * 1024;
-    // Pieces per pass: estimate, per candidate P, the cycles of the busiest CTA.  A pass is bound by the tensor pipe
-    // (an M = 128 MMA of N columns takes max(69, N / 2) cycles per K = 16, tools/probe/umma_rate_probe.cu) or by what one
-    // SM gets from L2 when all SMs pull at once (~23 B/cycle: 148 SMs x 23 B x 1.965 GHz = the ~6.6 TB/s the L2 delivers,
-    // measured on the residual layer: 382 KB per item in 8.6 us); with P = 1 the epilogue (~12 cycles per pixel column
-    // with 16 warps) hides behind the next pass, with P > 1 it does not.
-    static const int force_p = getenv("P2P_SWAP_PIECES") != nullptr ? atoi(getenv("P2P_SWAP_PIECES")) : 0;
-    const int bw = (Wv + 7) / 8, bh = (Hv + p.rows - 1) / p.rows;
-    const int items_per_ntile = bw * bh * N;
-    const int ncols = 8 * p.rows;
-    const double mma_cyc = (double)n_taps * p.c_chunks * (cin_blk / 16) * (ncols / 2 > 69 ? ncols / 2 : 69);
-    const double w_bytes = (double)n_taps * p.c_chunks * b_bytes, h_bytes = (double)p.c_chunks * p.HH * p.HW * rb;
-    double best = 0;
-    for (int cand = 1; cand <= 3; ++cand) {
-      if (cand * ncols > 512 || cand > items_per_ntile) break;
-      if (2 * cand * p.a_bytes + 3 * b_bytes + 1024 > 226 * 1024) break;
-      const int64_t passes = (int64_t)((items_per_ntile + cand - 1) / cand) * p.n_tiles;
-      const int per_cta = (int)((passes + kSMs - 1) / kSMs);
-      const double busy = passes < kSMs ? (double)passes : (double)kSMs;
-      const double ingest = (w_bytes + cand * h_bytes) / (23.0 * kSMs / busy);
-      const double pass_cyc = cand * mma_cyc > ingest ? cand * mma_cyc : ingest;
-      const double epi = 12.0 * ncols * cand;
-      const double total = cand == 1 ? per_cta * pass_cyc + epi : per_cta * (pass_cyc + epi);
-      if (force_p == cand || (force_p == 0 && (best == 0 || total < 0.97 * best))) {
-        best = total;
-        p.pieces = cand;
-      }
-    }
-    const int slot = p.pieces * p.a_bytes;
-    p.na = 2;
-    ring_budget = 225 * 1024 - p.na * slot - 1024;
+    ring_budget = 225 * 1024 - 2 * p.a_bytes - 1024;
   }
   int nb;
   if (p.resident) {
@@ -686,7 +624,7 @@ int run_halo_problem(const void* a_src, int N, int Hs, int Ws, int Ck, const voi
     if (nb < 2) return -2;
   }
   p.nb = nb;
-  const int smem = (swap ? p.na * p.pieces * p.a_bytes : 2 * p.a_bytes) + nb * b_bytes + (swap ? 0 : stg_bytes) + 1024;
+  const int smem = 2 * p.a_bytes + nb * b_bytes + (swap ? 0 : stg_bytes) + 1024;
   if (smem > 226 * 1024) return -2;
   p.n_taps = n_taps;
   for (int t = 0; t < n_taps; ++t) {
@@ -722,10 +660,8 @@ int run_halo_problem(const void* a_src, int N, int Hs, int Ws, int Ck, const voi
     if (int e = make_map_bf16(&mb, b_mat, 2, dims, strides, box, es, rb)) return e;
   }
   const int n_items = p.blocks_w * p.blocks_h * N * p.n_tiles;
-  int grid = n_items < kSMs ? n_items : kSMs;
+  const int grid = n_items < kSMs ? n_items : kSMs;
   if (swap) {
-    const int passes = ((p.blocks_w * p.blocks_h * N + p.pieces - 1) / p.pieces) * p.n_tiles;
-    grid = passes < kSMs ? passes : kSMs;
     switch (cin_blk) {
       case 16: return launch_halo_swap<16>(ma, mb, p, grid, smem, st);
       case 32: return launch_halo_swap<32>(ma, mb, p, grid, smem, st);
