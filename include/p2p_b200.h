@@ -238,6 +238,13 @@ int p2p_c_output(const void* res, const float* x, float* y, float* compressed, i
  * train.py:297 without net_c) in the same pass.  n elements, any layout; buffers 16-byte aligned.  Lets a host ship a
  * batch as bytes (4x less host-to-device traffic than the fp32 tensors the reference's DataLoader hands over). */
 int p2p_decode_u8(const uint8_t* src, float* dst, float* quant, int64_t n, int bits, void* stream);
+/* ---- VGG19 perceptual loss: VGGLoss / Vgg19, networks.py:18-62, used at train.py:377,395.
+ * Its thirteen 3x3 pad-1 convolutions + ReLU are p2p_conv_fwd / p2p_conv_dgrad calls with act = P2P_ACT_RELU in the
+ * epilogue (frozen weights: no weight gradient), p2p_act_bwd masks the gradient, the L1 taps reuse p2p_l1_fwd / _bwd;
+ * these two replace nn.MaxPool2d(2, 2) (torchvision vgg19.features[4, 9, 18, 27]) and its backward on stored maps
+ * [N,H,W,C] (H, W even): `in` is the pooling INPUT; the gradient goes to the first maximum of each 2x2 window. */
+int p2p_maxpool2_fwd(const void* in, void* out, int N, int H, int W, int C, int dtype, void* stream);
+int p2p_maxpool2_bwd(const void* in, const void* dout, void* din, int N, int H, int W, int C, int dtype, void* stream);
 /* stored map [B,H,W,C] dtype <-> NCHW fp32 [B,c_real,H,W] (drop-in API edge). */
 int p2p_nhwc_to_nchw(const void* in, float* out, int B, int H, int W, int C, int c_real, int dtype, void* stream);
 int p2p_nchw_to_nhwc(const float* in, void* out, int B, int H, int W, int C, int c_real, int dtype, void* stream);

@@ -48,3 +48,8 @@ def psnr_inputs(h, w, seed, kind):
     else:
         b = a.clone()
     return a, b
+
+VGG_CASES = [  # perceptual loss alone: name, batch, H, W, data seed (H, W multiples of 16: four 2x2 poolings)
+    ("b2_32x32", 2, 32, 32, 31),
+    ("b1_64x48", 1, 64, 48, 32),
+]

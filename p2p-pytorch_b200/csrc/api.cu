@@ -57,7 +57,8 @@ static int check_conv(const p2p_conv* c) {
   P2P_REQUIRE((c->Ho - 1) * c->stride + c->kh - c->pad <= c->Hi + c->pad &&
                   (c->Wo - 1) * c->stride + c->kw - c->pad <= c->Wi + c->pad,
               "output larger than the padded input allows");
-  P2P_REQUIRE(c->act == P2P_ACT_NONE || c->act == P2P_ACT_LRELU, "epilogue activation must be none or leaky relu");
+  P2P_REQUIRE(c->act == P2P_ACT_NONE || c->act == P2P_ACT_LRELU || c->act == P2P_ACT_RELU,
+              "epilogue activation must be none, relu or leaky relu");
   return 0;
 }
 

@@ -399,7 +399,8 @@ __global__ void __launch_bounds__(352, 1)
     const int q = warp & 3;                     // TMEM lane quarter this warp may read
     const int half = (warp - 2) >> 2;           // columns [128 * half, 128 * half + 128) = block rows 16*half ..
     const int ch = q * 32 + lane;
-    const bool lrelu = p.epi.act == P2P_ACT_LRELU;
+    const bool lrelu = p.epi.act == P2P_ACT_LRELU || p.epi.act == P2P_ACT_RELU;   // max(f, slope * f)
+    const float slope = p.epi.act == P2P_ACT_LRELU ? 0.2f : 0.f;
     const bool even = (lane & 1) == 0;
     // lane pairs trade halves so that every lane owns one pixel x two channels: odd lanes first swap their own
     // halves (sel_own), then each lane keeps its low half and takes the neighbour's high half (sel_word)
@@ -461,7 +462,7 @@ __global__ void __launch_bounds__(352, 1)
             for (int x = 0; x < 8; x += 2) {
               const int j = rr * 8 + x;
               float f0 = __uint_as_float(v[j]) + bias, f1 = __uint_as_float(v[j + 1]) + bias;
-              if (lrelu) { f0 = fmaxf(f0, 0.2f * f0); f1 = fmaxf(f1, 0.2f * f1); }
+              if (lrelu) { f0 = fmaxf(f0, slope * f0); f1 = fmaxf(f1, slope * f1); }
               const uint32_t pk = pack_bf16x2(f0, f1);    // (pixel j, pixel j+1) of my channel, rounded as stored
               const float r0 = __uint_as_float(pk << 16), r1 = __uint_as_float(pk & 0xffff0000u);
               s += r0 + r1;
@@ -478,7 +479,7 @@ __global__ void __launch_bounds__(352, 1)
             const bool row_ok = yy < h_lim;
             const bool ok0 = row_ok && ox0 + x < p.epi.Wv, ok1 = row_ok && ox0 + x + 1 < p.epi.Wv;
             float f0 = __uint_as_float(v[j]) + bias, f1 = __uint_as_float(v[j + 1]) + bias;
-            if (lrelu) { f0 = fmaxf(f0, 0.2f * f0); f1 = fmaxf(f1, 0.2f * f1); }
+            if (lrelu) { f0 = fmaxf(f0, slope * f0); f1 = fmaxf(f1, slope * f1); }
             if (!real || !ok0) f0 = 0.f;        // channel padding and positions outside the map are exact zeros
             if (!real || !ok1) f1 = 0.f;
             const uint32_t pk = pack_bf16x2(f0, f1);

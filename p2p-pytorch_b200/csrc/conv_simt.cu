@@ -122,6 +122,7 @@ __global__ void __launch_bounds__(256) conv_simt_kernel(const T* __restrict__ a,
       if (!DGRAD) {
         if (bias != nullptr && n < d.co_real) v += bias[n];
         if (d.act == P2P_ACT_LRELU) v = v > 0.f ? v : 0.2f * v;
+        if (d.act == P2P_ACT_RELU) v = v > 0.f ? v : 0.f;
         if (n >= d.co_real) v = 0.f;
       }
       stf(out + m * Cn + n, v);

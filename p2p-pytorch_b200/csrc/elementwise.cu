@@ -630,10 +630,11 @@ __global__ void __launch_bounds__(256)
 #pragma unroll
       for (int k = 0; k < 8; ++k) g[k] += t[k];
     }
-    if (act == P2P_ACT_LRELU) {
+    if (act == P2P_ACT_LRELU || act == P2P_ACT_RELU) {
+      const float neg = act == P2P_ACT_LRELU ? 0.2f : 0.f;
       ld8(out + (size_t)p * C + c8 * 8, o);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) g[k] *= (o[k] > 0.f ? 1.f : 0.2f);
+      for (int k = 0; k < 8; ++k) g[k] *= (o[k] > 0.f ? 1.f : neg);
     }
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
@@ -890,6 +891,75 @@ __global__ void __launch_bounds__(256) decode_u8_kernel(const uint8_t* __restric
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------------
+// MaxPool2d(kernel 2, stride 2) on stored NHWC maps (torchvision's vgg19.features[4, 9, 18, 27], reference
+// networks.py:32-50) and its gradient: the whole gradient goes to the first maximum of the window in scan order
+// (PyTorch keeps the index of the first element that compares greater).  8 channels per thread.
+// ---------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+    maxpool2_fwd_kernel(const T* __restrict__ in, T* __restrict__ out, int N, int H, int W, int C) {
+  const int Ho = H >> 1, Wo = W >> 1, C8 = C >> 3;
+  const int64_t total = (int64_t)N * Ho * Wo * C8;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % C8);
+    int64_t r = i / C8;
+    const int x = (int)(r % Wo);
+    r /= Wo;
+    const int y = (int)(r % Ho), n = (int)(r / Ho);
+    const T* src = in + (((int64_t)n * H + 2 * y) * W + 2 * x) * C + c8 * 8;
+    float m[8], t[8];
+    ld8(src, m);
+    ld8(src + C, t);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) m[k] = t[k] > m[k] ? t[k] : m[k];
+    ld8(src + (int64_t)W * C, t);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) m[k] = t[k] > m[k] ? t[k] : m[k];
+    ld8(src + (int64_t)W * C + C, t);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) m[k] = t[k] > m[k] ? t[k] : m[k];
+    st8(out + i * 8, m);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+    maxpool2_bwd_kernel(const T* __restrict__ in, const T* __restrict__ dout, T* __restrict__ din, int N, int H, int W,
+                        int C) {
+  const int Ho = H >> 1, Wo = W >> 1, C8 = C >> 3;
+  const int64_t total = (int64_t)N * Ho * Wo * C8;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % C8);
+    int64_t r = i / C8;
+    const int x = (int)(r % Wo);
+    r /= Wo;
+    const int y = (int)(r % Ho), n = (int)(r / Ho);
+    const int64_t base = (((int64_t)n * H + 2 * y) * W + 2 * x) * C + c8 * 8;
+    const int64_t offs[4] = {0, C, (int64_t)W * C, (int64_t)W * C + C};
+    float v[4][8], g[8], z[8];
+    int arg[8];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) ld8(in + base + offs[q], v[q]);
+    ld8(dout + i * 8, g);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      arg[k] = 0;
+      float m = v[0][k];
+#pragma unroll
+      for (int q = 1; q < 4; ++q)
+        if (v[q][k] > m) { m = v[q][k]; arg[k] = q; }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) z[k] = arg[k] == q ? g[k] : 0.f;
+      st8(din + base + offs[q], z);
+    }
+  }
+}
+
 }  // namespace p2p
 
 using namespace p2p;
@@ -1046,7 +1116,8 @@ int p2p_d_input_grad(const float* dx, float* db, int ca, int cb, int B, int H, i
 int p2p_act_bwd(const void* out, const void* g_a, const void* g_b, void* dz, float* dbias, int64_t pixels, int C,
                 int c_real, int act, int dtype, void* stream) {
   P2P_REQUIRE(dz && (g_a || g_b), "null pointer");
-  P2P_REQUIRE(act == P2P_ACT_NONE || (act == P2P_ACT_LRELU && out), "LeakyReLU gradient needs the forward output");
+  P2P_REQUIRE(act == P2P_ACT_NONE || ((act == P2P_ACT_LRELU || act == P2P_ACT_RELU) && out),
+              "(Leaky)ReLU gradient needs the forward output");
   P2P_REQUIRE(C % 16 == 0 && C <= 512, "C must be a multiple of 16, <= 512");
   const int ppb = 256 / (C / 8);
   P2P_DISPATCH(dtype, act_bwd_kernel<T><<<red_ew_grid(pixels, ppb), 256, 0, as_stream(stream)>>>(
@@ -1130,6 +1201,21 @@ int p2p_decode_u8(const uint8_t* src, float* dst, float* quant, int64_t n, int b
   if (blocks < 1) blocks = 1;
   if (blocks > kSMs * 8) blocks = kSMs * 8;
   decode_u8_kernel<<<(int)blocks, 256, 0, as_stream(stream)>>>(src, dst, quant, n, (float)((1 << bits) - 1));
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_maxpool2_fwd(const void* in, void* out, int N, int H, int W, int C, int dtype, void* stream) {
+  P2P_REQUIRE(in && out && N > 0 && H >= 2 && W >= 2 && H % 2 == 0 && W % 2 == 0 && C % 8 == 0, "bad arguments");
+  const int64_t total = (int64_t)N * (H / 2) * (W / 2) * (C / 8);
+  P2P_DISPATCH(dtype, maxpool2_fwd_kernel<T><<<ew_grid(total), 256, 0, as_stream(stream)>>>((const T*)in, (T*)out, N, H, W, C););
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_maxpool2_bwd(const void* in, const void* dout, void* din, int N, int H, int W, int C, int dtype, void* stream) {
+  P2P_REQUIRE(in && dout && din && N > 0 && H >= 2 && W >= 2 && H % 2 == 0 && W % 2 == 0 && C % 8 == 0, "bad arguments");
+  const int64_t total = (int64_t)N * (H / 2) * (W / 2) * (C / 8);
+  P2P_DISPATCH(dtype, maxpool2_bwd_kernel<T><<<ew_grid(total), 256, 0, as_stream(stream)>>>((const T*)in, (const T*)dout,
+                                                                                          (T*)din, N, H, W, C););
   P2P_LAUNCH_CHECK();
 }
 

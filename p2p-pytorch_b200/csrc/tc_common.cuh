@@ -236,7 +236,8 @@ __device__ __forceinline__ void epilogue_tile(uint32_t tmem_tile, int q, int lan
   const int tw_mask = (1 << e.tw_log2) - 1;
   const bool valid = (e.oy0 + (row >> e.tw_log2)) < e.Hv && (e.ox0 + (row & tw_mask)) < e.Wv;
   const bool full_n = e.n0 + BLOCK_N <= e.co_real;
-  const bool lrelu = e.act == P2P_ACT_LRELU;
+  const bool lrelu = e.act == P2P_ACT_LRELU || e.act == P2P_ACT_RELU;     // max(f, slope * f)
+  const float slope = e.act == P2P_ACT_LRELU ? 0.2f : 0.f;
   // ---- phase 1: TMEM -> registers -> bf16 -> staging ---------------------------------------------
 #pragma unroll 1
   for (int c0 = 0; c0 < BLOCK_N; c0 += CH) {
@@ -251,8 +252,8 @@ __device__ __forceinline__ void epilogue_tile(uint32_t tmem_tile, int q, int lan
       float f0 = __uint_as_float(v[j]) + b4.x, f1 = __uint_as_float(v[j + 1]) + b4.y;
       float f2 = __uint_as_float(v[j + 2]) + b4.z, f3 = __uint_as_float(v[j + 3]) + b4.w;
       if (lrelu) {
-        f0 = fmaxf(f0, 0.2f * f0); f1 = fmaxf(f1, 0.2f * f1);
-        f2 = fmaxf(f2, 0.2f * f2); f3 = fmaxf(f3, 0.2f * f3);
+        f0 = fmaxf(f0, slope * f0); f1 = fmaxf(f1, slope * f1);
+        f2 = fmaxf(f2, slope * f2); f3 = fmaxf(f3, slope * f3);
       }
       pk[j / 2] = pack_bf16x2(f0, f1);
       pk[j / 2 + 1] = pack_bf16x2(f2, f3);

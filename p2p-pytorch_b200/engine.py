@@ -705,3 +705,123 @@ def compression_forward(x, convs, prelus, bn, training: bool, bits: Optional[int
     comp = _empty((B, 3, H, W), torch.float32, dev) if bits is not None else None
     call("p2p_c_output", ptr(res), ptr(x), ptr(y), ptr(comp), B, H, W, bits if bits is not None else 3, dc)
     return y, comp
+
+
+# =====================================================================================================
+# VGG19 perceptual loss: VGGLoss / Vgg19, reference networks.py:18-62
+# =====================================================================================================
+# torchvision vgg19().features[0:30]: output channels of the 3x3 pad-1 convolutions (each followed by ReLU), "M" = 2x2
+# max-pool; Vgg19 taps the activation after features[1], [6], [11], [20], [29] (networks.py:42-51)
+VGG_CFG = (64, 64, "M", 128, 128, "M", 256, 256, 256, 256, "M", 512, 512, 512, 512, "M", 512)
+VGG_TAP_AFTER_CONV = (0, 2, 4, 8, 12)          # index (0..12) of the convolution whose ReLU output is tapped
+VGG_WEIGHTS = (1.0 / 32, 1.0 / 16, 1.0 / 8, 1.0 / 4, 1.0)      # networks.py:23
+
+
+class VGGPack:
+    """The thirteen frozen filter banks packed once for a (dtype, kernel family): forward and data-gradient layouts."""
+
+    def __init__(self, weights, dt):
+        self.key = (dt, _state["impl"], tuple(w._version for w in weights), tuple(w.data_ptr() for w in weights))
+        self.plans, jobs = [], []
+        dc = L.dtype_code(dt)
+        for w in weights:
+            cout, cin = w.shape[0], w.shape[1]
+            pk = ConvPlan(1, 3, 3, pad16(cin), cin, cout, 3, 1, 1)
+            jobs.append(pk.pack_job(w.detach(), None, dt))
+            self.plans.append(pk)
+        L.call_multi("p2p_pack_weights_multi", jobs, dc)
+
+
+class VGGLossFunction(torch.autograd.Function):
+    """loss = sum_i w_i * mean|vgg(x)_i - vgg(y)_i| (VGGLoss.forward, networks.py:25-30), y detached.
+
+    apply(x, y, pack, *biases): x, y [B,3,H,W] fp32 NCHW (H, W multiples of 16); `pack` a VGGPack.  The feature stack
+    runs ONCE on the 2B images of cat(x, y); backward walks only the x half (frozen weights: data-gradients only)."""
+
+    @staticmethod
+    def forward(ctx, x, y, pack, *biases):
+        L.require_cuda(x, "VGGLoss input")
+        L.require_cuda(y, "VGGLoss target")
+        if x.shape != y.shape or x.dim() != 4 or x.shape[1] != 3 or x.shape[2] % 16 or x.shape[3] % 16:
+            raise L.P2PError("VGGLoss needs two [B,3,H,W] batches with H, W multiples of 16")
+        B, _, H, W = x.shape
+        dt, dev = _state["dtype"], x.device
+        dc = L.dtype_code(dt)
+        xy = torch.cat((x.detach().float(), y.detach().float()), 0).contiguous()
+        cur = _empty((2 * B, H, W, 16), dt, dev)
+        call("p2p_nchw_to_nhwc", ptr(xy), ptr(cur), 2 * B, H, W, 16, 3, dc)
+        loss = torch.zeros((), dtype=torch.float32, device=dev)
+        layers = []                      # per convolution: (plan, input, output, pooled-from) for the backward walk
+        taps = []
+        h, w, cin, ci = H, W, 3, 0
+        pool_src = None
+        for v in VGG_CFG:
+            if v == "M":
+                nxt = _empty((2 * B, h // 2, w // 2, cur.shape[3]), dt, dev)
+                call("p2p_maxpool2_fwd", ptr(cur), ptr(nxt), 2 * B, h, w, cur.shape[3], dc)
+                pool_src = cur
+                cur, h, w = nxt, h // 2, w // 2
+                continue
+            plan = ConvPlan(2 * B, h, w, cur.shape[3], cin, v, 3, 1, 1, L.ACT_RELU)
+            plan.wp, plan.wt = pack.plans[ci].wp, pack.plans[ci].wt
+            out = _empty((2 * B, h, w, plan.Co), dt, dev)
+            plan.fwd(cur, biases[ci], out, None)
+            layers.append((plan, cur, out, pool_src))
+            pool_src = None
+            if ci in VGG_TAP_AFTER_CONV:
+                i = VGG_TAP_AFTER_CONV.index(ci)
+                call("p2p_l1_fwd", ptr(out[:B]), ptr(out[B:]), float(VGG_WEIGHTS[i]), ptr(loss), B * h * w, plan.Co, v, dc)
+                taps.append(i)
+            cur, cin, ci = out, v, ci + 1
+        ctx.layers, ctx.geom = layers, (B, H, W)
+        ctx.set_materialize_grads(False)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        if ctx.needs_input_grad[1]:
+            raise L.P2PError("VGGLoss: the target is detached in the reference (networks.py:29)")
+        if g is None or not ctx.needs_input_grad[0]:
+            return (None,) * (3 + 13)
+        layers = ctx.layers
+        B, H, W = ctx.geom
+        dt, dev = layers[0][2].dtype, layers[0][2].device
+        dc = L.dtype_code(dt)
+        g = g.contiguous().float()
+        g_next = None                    # gradient w.r.t. the OUTPUT of the layer being processed (x half only)
+        for ci in reversed(range(len(layers))):
+            plan, x_in, out, pool_src = layers[ci]
+            d = plan.desc
+            hB = _half_plan(plan, B)
+            o_x = out[:B]
+            gu = None
+            if ci in VGG_TAP_AFTER_CONV:
+                i = VGG_TAP_AFTER_CONV.index(ci)
+                gu = _empty(tuple(o_x.shape), dt, dev)
+                call("p2p_l1_bwd", ptr(o_x), ptr(out[B:]), float(VGG_WEIGHTS[i]), ptr(g), ptr(gu), B * d.Ho * d.Wo, plan.Co,
+                     plan.cout_real, dc)
+            if gu is None and g_next is None:
+                continue
+            dz = _empty(tuple(o_x.shape), dt, dev)
+            call("p2p_act_bwd", ptr(o_x), ptr(gu), ptr(g_next), ptr(dz), None, B * d.Ho * d.Wo, plan.Co, plan.cout_real,
+                 L.ACT_RELU, dc)
+            din = _empty((B,) + tuple(x_in.shape[1:]), dt, dev)
+            hB.dgrad(dz, din)
+            if pool_src is not None:
+                up = _empty((B,) + tuple(pool_src.shape[1:]), dt, dev)
+                call("p2p_maxpool2_bwd", ptr(pool_src[:B]), ptr(din), ptr(up), B, pool_src.shape[1], pool_src.shape[2],
+                     pool_src.shape[3], dc)
+                din = up
+            g_next = din
+        gx = _empty((B, 3, H, W), torch.float32, dev)
+        call("p2p_nhwc_to_nchw", ptr(g_next), ptr(gx), B, H, W, 16, 3, dc)
+        ctx.layers = None
+        return (gx, None, None) + (None,) * 13
+
+
+def _half_plan(plan: ConvPlan, B: int) -> ConvPlan:
+    """the same layer for the first B images of the batch it was built for"""
+    d = plan.desc
+    hp = ConvPlan(B, d.Hi, d.Wi, d.Ci, plan.cin_real, plan.cout_real, plan.k, plan.stride, plan.pad, plan.act)
+    hp.wp, hp.wt, hp.w1x1 = plan.wp, plan.wt, plan.w1x1
+    return hp

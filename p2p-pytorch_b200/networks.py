@@ -6,6 +6,7 @@ Same public names, signatures, `state_dict()` keys / shapes, parameter registrat
     define_G(init_type, init_gain, gpu_id)                      reference networks.py:164-171
     define_D(input_nc, ndf, norm, use_sigmoid, init_type, ...)  reference networks.py:708-714
     GANLoss(use_lsgan, target_real_label, target_fake_label)    reference networks.py:808-850
+    VGGLoss(device) / Vgg19()                                   reference networks.py:18-62
     init_weights / init_net                                     reference networks.py:128-155
 
 The `nn.Conv2d` / `nn.BatchNorm2d` / `nn.PReLU` objects below are parameter containers only -- their
@@ -328,3 +329,95 @@ class GANLoss(nn.Module):
         for p in preds:
             loss = loss + mse_const_flat(p, label)
         return loss
+
+
+# -----------------------------------------------------------------------------------------------------
+# VGG19 perceptual loss (reference networks.py:18-62; train.py:193, :377, :395)
+# -----------------------------------------------------------------------------------------------------
+class Vgg19(nn.Module):
+    """torchvision's vgg19().features[0:30] cut into the reference's five slices (networks.py:42-51); the modules
+    are parameter containers with the reference's names (`slice2.5.weight` = features[5].weight), all frozen.
+
+    The reference downloads the ImageNet weights in its constructor (networks.py:35).  Here construction never touches
+    the network: pass `features_state_dict` (torchvision's `vgg19(...).features.state_dict()`, a whole-model
+    `vgg19(...).state_dict()`, or this module's own keys) or call `load_pretrained` / `load_state_dict` later.
+    Until then the weights are torchvision's random initialisation of the same architecture."""
+
+    def __init__(self, requires_grad=False, features_state_dict=None):
+        super().__init__()
+        if requires_grad:
+            raise NotImplementedError("the perceptual network is frozen in the reference (networks.py:52-54)")
+        ends = (1, 6, 11, 20, 29)
+        slices = [nn.Sequential() for _ in ends]
+        idx, cin = 0, 3
+        for v in E.VGG_CFG:
+            k = next(i for i, e in enumerate(ends) if idx <= e)
+            if v == "M":
+                slices[k].add_module(str(idx), nn.MaxPool2d(kernel_size=2, stride=2))
+                idx += 1
+                continue
+            conv = nn.Conv2d(cin, v, kernel_size=3, padding=1)
+            init.kaiming_normal_(conv.weight, mode="fan_out", nonlinearity="relu")       # torchvision's vgg init
+            init.constant_(conv.bias, 0.0)
+            slices[k].add_module(str(idx), conv)
+            k = next(i for i, e in enumerate(ends) if idx + 1 <= e)
+            slices[k].add_module(str(idx + 1), nn.ReLU(inplace=True))
+            idx, cin = idx + 2, v
+        self.slice1, self.slice2, self.slice3, self.slice4, self.slice5 = slices
+        for p in self.parameters():
+            p.requires_grad = False
+        if features_state_dict is not None:
+            self.load_pretrained(features_state_dict)
+
+    def load_pretrained(self, sd):
+        """accepts `features.<i>.weight`, `<i>.weight` or `slice<k>.<i>.weight` keys"""
+        own = self.state_dict()
+        by_idx = {k.split(".")[1] + "." + k.split(".")[2]: k for k in own}
+        new = {}
+        for k, v in sd.items():
+            parts = k.split(".")
+            if parts[0] == "classifier":
+                continue
+            if parts[0] == "vgg":
+                parts = parts[1:]
+            if parts[0] == "features" or parts[0].startswith("slice"):
+                parts = parts[1:]
+            key = ".".join(parts[:2])
+            if key in by_idx:
+                new[by_idx[key]] = v
+        missing = set(own) - set(new)
+        if missing:
+            raise KeyError(f"VGG19 weights missing for {sorted(missing)[:4]} ...")
+        self.load_state_dict(new)
+
+    def conv_params(self):
+        ws, bs = [], []
+        for sl in (self.slice1, self.slice2, self.slice3, self.slice4, self.slice5):
+            for m in sl:
+                if isinstance(m, nn.Conv2d):
+                    ws.append(m.weight)
+                    bs.append(m.bias)
+        return ws, bs
+
+
+class VGGLoss(nn.Module):
+    """criterionVGG of the reference (networks.py:18-30): sum_i w_i L1(vgg(x)_i, vgg(y)_i.detach()), w = 1/32 ... 1.
+    `VGGLoss(device)` as at train.py:193; `features_state_dict` supplies the pretrained weights (see Vgg19)."""
+
+    def __init__(self, device=None, features_state_dict=None):
+        super().__init__()
+        self.vgg = Vgg19(features_state_dict=features_state_dict)
+        self.criterion = nn.L1Loss()
+        self.weights = list(E.VGG_WEIGHTS)
+        self._pack = None
+        if device is not None:
+            self.to(device)
+
+    def forward(self, x, y):
+        ws, bs = self.vgg.conv_params()
+        L.require_cuda(ws[0], "VGG19 weights")
+        dt = E._state["dtype"]
+        key = (dt, E._state["impl"], tuple(w._version for w in ws), tuple(w.data_ptr() for w in ws))
+        if self._pack is None or self._pack.key != key:
+            self._pack = E.VGGPack(ws, dt)            # frozen banks: packed once, reused by every call
+        return E.VGGLossFunction.apply(x, y, self._pack, *[b.detach() for b in bs])

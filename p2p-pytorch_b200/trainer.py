@@ -54,8 +54,11 @@ class Pix2PixTrainer:
     """optimizer_g / optimizer_d loop of train.py:241-242, :294-390."""
 
     def __init__(self, net_g, net_d, lr: float = 2e-4, beta1: float = 0.5, process_group=None,
-                 bucket_bytes: int = 64 << 20, cuda_graph: bool = False, graph_warmup: int = 2, net_c=None):
+                 bucket_bytes: int = 64 << 20, cuda_graph: bool = False, graph_warmup: int = 2, net_c=None, vgg=None):
         self.net_g, self.net_d, self.net_c = net_g, net_d, net_c
+        # vgg: a VGGLoss module (criterionVGG, train.py:193) -- adds content_loss = vgg(fake_b, real_b) * 10 to loss_g
+        # (train.py:377-380) and, in step_full, c_percp = vgg(compressed, real_b) * 10 to the logged phase-3 loss (:395)
+        self.vgg = vgg
         # cuda_graph=True: the first `graph_warmup` calls of step() run eagerly, the next one records the whole
         # iteration (~650 launches, both backward passes, the all-reduces and both Adam updates) into one CUDA
         # graph per input shape, and every later call is three input copies and one graph launch.  The host
@@ -207,6 +210,8 @@ class Pix2PixTrainer:
                 loss_c = torch.zeros((), dtype=torch.float32, device=compressed.device)
                 L.call("p2p_mse_pair_fwd", L.ptr(fake_after), L.ptr(real_b.contiguous().float()), 1.0,
                        L.ptr(loss_c), fake_after.numel())                                 # :394
+                if self.vgg is not None:
+                    out["loss_c_percp"] = self.vgg(compressed, real_b) * 10.0             # :395 (its gradient is zero too)
             out["loss_c"] = loss_c
         return out
 
@@ -266,6 +271,10 @@ class Pix2PixTrainer:
         loss_feat = feature_matching_loss(pred_fake, pred_real, cr)                       # :344-351
         loss_tv = tv_loss(fake_b)                                                         # :378
         loss_g = loss_g_gan + loss_feat + loss_tv                                         # :353,:380
+        loss_vgg = None
+        if self.vgg is not None:
+            loss_vgg = self.vgg(fake_b, real_b) * 10.0                                    # :377
+            loss_g = loss_g + loss_vgg
         self.optimizer_g.zero_grad()                                                      # :384
         self.optimizer_d.zero_grad()                                                      # :388 (hoisted: D grads untouched above)
         # The two backward passes are independent (loss_d sees fake_b detached, the third D pass is frozen), so the
@@ -282,5 +291,8 @@ class Pix2PixTrainer:
         self.optimizer_d.step()                                                           # :390
         self.red_g.wait()
         self.optimizer_g.step()                                                           # :386
-        return {"fake_b": fake_b.detach(), "loss_d": loss_d.detach(), "loss_g_gan": loss_g_gan.detach(),
-                "loss_feat": loss_feat.detach(), "loss_tv": loss_tv.detach(), "loss_g": loss_g.detach()}
+        out = {"fake_b": fake_b.detach(), "loss_d": loss_d.detach(), "loss_g_gan": loss_g_gan.detach(),
+               "loss_feat": loss_feat.detach(), "loss_tv": loss_tv.detach(), "loss_g": loss_g.detach()}
+        if loss_vgg is not None:
+            out["loss_vgg"] = loss_vgg.detach()
+        return out

@@ -301,42 +301,53 @@ def test_state_dict_interchange_and_eval_mode():
         g(torch.zeros(1, 3, 32, 32))                      # CPU tensor: no fallback path
 
 
-def test_loss_curves_track_oracle_200_steps():
-    """north star: loss curves track the reference over 200 steps (fp32 verification mode, batch 2, 32x32).
+@pytest.mark.parametrize("precision,graph", [("bf16", True), ("bf16", False), ("fp32", False)],
+                         ids=["bf16-graph", "bf16-eager", "fp32-eager"])
+def test_loss_curves_track_oracle_200_steps(precision, graph):
+    """north star: loss curves track the reference over 200 steps -- in the precision and launch mode the benchmark
+    runs (bf16, tcgen05 kernels, CUDA-graph replay), and in the fp32 verification mode.
 
-    What "track" can mean is bounded by the reference's own sensitivity: two runs of the ORACLE whose initial
-    weights differ by 1e-6 relative noise agree to 4 digits for ~10 steps and then drift apart by up to 38% in
-    the 20-step means of loss_d (19% for loss_g) between steps 40 and 140 before re-converging
-    (tests/diagnostics/oracle_self_divergence.py -> profiles/oracle_self_divergence_200.npz): GAN dynamics at batch 2
-    amplify rounding differences.  So: pointwise agreement while the trajectories are still the same one,
-    window means within 1.5x the oracle's own spread afterwards, and the same overall level."""
-    steps = 200
-    P, g, d = build("fp32")
-    tr = P.Pix2PixTrainer(g, d)
-    ot = orc.OracleTrainer(orc.init_g_state(123), orc.init_d_state(124))
-    mine, ref = [], []
+    GAN training amplifies rounding noise: runs of the ORACLE itself whose initial weights differ by bf16-rounding-size
+    noise separate after ~10 iterations.  oracle/make_envelope.py therefore ran the oracle six times at batch 8, 64x64
+    (stock init + five perturbed inits, same 200 batches) and committed every per-step loss
+    (tests/golden/oracle_envelope_b8_64x64_200.npz: 25-step window means of loss_d spread by 5-27 %, of loss_g by
+    6-20 % between those runs).  Those six runs understate the tails: the fp32 verification mode -- exact arithmetic,
+    losses equal to the oracle's to 1e-5 at step 0 -- leaves the one-range-widened [min, max] band in 2 of 16 windows
+    (by up to 13 % of the window's median) and the bf16 path in 1 (a phase where D is ahead: loss_d -15 %, loss_g +29 %;
+    profiles/r02c_loss_curves_200_*.npz).  Bounds, calibrated on that: (1) pointwise agreement with the unperturbed
+    oracle run while the trajectories are still one (first 3 steps, 1e-3 relative; measured 1e-5 ... 4e-4);
+    (2) every 25-step window mean of loss_d and loss_g within 35 % of the oracle's median for that window, and at least
+    6 of the 8 windows of each loss inside the oracle's [min, max] widened by one range on each side; (3) the 200-step
+    means within 10 % of the oracle's (its own runs differ by 3.5 %).  A path that trained 1.5x worse or better than the
+    reference fails (2) in most windows and (3) outright."""
+    env = np.load(os.path.join(GOLD, "oracle_envelope_b8_64x64_200.npz"))
+    curves = env["curves"][:, :, :2]                      # [runs, steps, (loss_d, loss_g)]
+    batch, size, seed0, steps = int(env["batch"]), int(env["size"]), int(env["data_seed"]), curves.shape[1]
+    P, g, d = build(precision)
+    tr = P.Pix2PixTrainer(g, d, cuda_graph=graph, graph_warmup=1)
+    mine = []
     for it in range(steps):
-        a, b, c = orc.synthetic_batch(2, 32, 32, 1000 + it)
+        a, b, c = orc.synthetic_batch(batch, size, size, seed0 + it)
         o = tr.step(a.to(DEV), b.to(DEV), c.to(DEV))
-        r = ot.step(a, b, c)
-        mine.append([o[k].item() for k in ("loss_d", "loss_g")])
-        ref.append([r[k].item() for k in ("loss_d", "loss_g")])
-    mine, ref = np.array(mine), np.array(ref)
+        mine.append([o["loss_d"].item(), o["loss_g"].item()])
+    mine = np.array(mine)
     os.makedirs("gpurun_out", exist_ok=True)
-    np.savez("gpurun_out/loss_curves_200.npz", mine=mine, ref=ref)
+    np.savez(f"gpurun_out/loss_curves_200_{precision}_{'graph' if graph else 'eager'}.npz", mine=mine, oracle=curves)
     assert np.isfinite(mine).all()
-    assert np.all(np.abs(mine[:8] - ref[:8]) <= 1e-2 * np.abs(ref[:8])), (mine[:8], ref[:8])
-    # 25-step windows: once the two trajectories have separated, a window of loss_d can catch one run in a phase
-    # where D is winning and the other not (seen once in ~15 runs: 0.09 against 0.42).  So: most windows within
-    # 75 % (1.5x the oracle's own 20-step spread), every window within a factor of 8 (no blow-up, no collapse).
-    close = []
-    for lo in range(0, steps, 25):
-        m, r = mine[lo:lo + 25].mean(0), ref[lo:lo + 25].mean(0)
-        assert np.all(m <= 8 * r) and np.all(r <= 8 * m), (lo, m, r)
-        close.append(bool(np.all(np.abs(m - r) <= 0.75 * np.abs(r))))
-    assert sum(close) >= len(close) - 2, close
-    m, r = mine.mean(0), ref.mean(0)
-    assert np.all(np.abs(m - r) <= 0.4 * np.abs(r)), (m, r)      # two oracle runs differ by up to ~0.3 here
+    if graph:
+        assert len(tr._graphs) == 1 and tr.graph_launches > 100
+    assert np.all(np.abs(mine[:3] - curves[0, :3]) <= 1e-3 * np.abs(curves[0, :3])), (mine[:3], curves[0, :3])
+    win = 25
+    w_or = curves.reshape(curves.shape[0], steps // win, win, 2).mean(2)           # [runs, windows, 2]
+    w_me = mine.reshape(steps // win, win, 2).mean(1)
+    med, lo, hi = np.median(w_or, 0), w_or.min(0), w_or.max(0)
+    rel = np.abs(w_me - med) / med
+    assert np.all(rel <= 0.35), (np.round(rel, 3).tolist(), np.round(w_me, 3).tolist(), np.round(med, 3).tolist())
+    inside = (w_me >= lo - (hi - lo)) & (w_me <= hi + (hi - lo))
+    assert np.all(inside.sum(0) >= inside.shape[0] - 2), (np.round(w_me, 3).tolist(), np.round(lo, 3).tolist(),
+                                                          np.round(hi, 3).tolist())
+    m_or, m_me = curves.mean(1).mean(0), mine.mean(0)
+    assert np.all(np.abs(m_me - m_or) <= 0.10 * m_or), (m_me, m_or)
 
 
 # ---- compression front end (SURVEY 8f row 1) -----------------------------------------------------------------------
@@ -453,3 +464,78 @@ def test_psnr_on_device_is_exact():
     got = P.psnr(a.to(DEV), b.to(DEV)).cpu().numpy()
     want = np.array([orc.psnr(a[i:i + 1], b[i:i + 1]) for i in range(5)])
     assert np.allclose(got, want, rtol=1e-12, atol=0)
+
+
+# ---- VGG19 perceptual loss --------------------------------------------------------------------------
+from oracle.make_golden_util import VGG_CASES  # noqa: E402
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+@pytest.mark.parametrize("case", VGG_CASES, ids=[c[0] for c in VGG_CASES])
+def test_vgg_loss_matches_reference_golden(case, precision):
+    """P.VGGLoss against vectors from the reference's own VGGLoss / Vgg19 classes holding the same seeded weights
+    (oracle/make_golden_vgg.py): loss, gradient w.r.t. the generated image, the five tapped activations."""
+    import p2p_pytorch_b200 as P
+    from p2p_pytorch_b200 import engine as E
+    name, batch, h, w, seed = case
+    gold = np.load(os.path.join(GOLD, f"ref_vgg_{name}.npz"))
+    P.set_precision(precision)
+    crit = P.VGGLoss(DEV)
+    crit.load_state_dict(orc.init_vgg_state(126))
+    a, b, _ = orc.synthetic_batch(batch, h, w, seed)
+    x = torch.tanh(a * 1.5).to(DEV).requires_grad_(True)
+    loss = crit(x, b.to(DEV))
+    loss.backward()
+    # the oracle's restatement agrees with the reference vectors too (CPU side of the same pin)
+    xo = torch.tanh(a * 1.5).requires_grad_(True)
+    lo = orc.vgg_loss(orc.init_vgg_state(126), xo, b)
+    lo.backward()
+    assert abs(lo.item() - float(gold["loss"])) <= 1e-5 * abs(float(gold["loss"]))
+    assert relerr(xo.grad, torch.from_numpy(gold["grad_x"])) <= 1e-4
+    if precision == "fp32":
+        assert abs(loss.item() - float(gold["loss"])) <= 1e-4 * abs(float(gold["loss"])), (loss.item(), float(gold["loss"]))
+        assert relerr(x.grad, torch.from_numpy(gold["grad_x"])) <= 2e-3
+        assert rms_relerr(x.grad, torch.from_numpy(gold["grad_x"])) <= 5e-4
+    else:
+        # bf16 operands through 13 convolutions: loss to 1e-2 (the north star's bf16 example).  The gradient image is
+        # compared by direction: four max-pools route each gradient to the arg-max of a 2x2 window, and where the two
+        # largest activations of a window differ by less than a bf16 rounding step (~1-2 % of the windows) the winner
+        # changes, which moves that gradient to the neighbouring pixel -- measured 0.24 rms on the 32x32 case, all of it
+        # such displaced entries (the fp32 mode meets 5e-4)
+        assert abs(loss.item() - float(gold["loss"])) <= 1e-2 * abs(float(gold["loss"])), (loss.item(), float(gold["loss"]))
+        assert rms_relerr(x.grad, torch.from_numpy(gold["grad_x"])) <= 0.35
+        assert cosine(x.grad, torch.from_numpy(gold["grad_x"])) >= 0.93
+    assert x.grad.shape == x.shape and x.grad.dtype == torch.float32
+
+
+@pytest.mark.parametrize("graph", [False, True], ids=["eager", "graph"])
+def test_train_step_with_vgg_matches_reference_golden(graph):
+    """One whole iteration with the perceptual term on (train.py:377-380), fp32 mode, against the unmodified reference."""
+    import p2p_pytorch_b200 as P
+    from oracle.make_golden_util import fingerprint
+    gold = np.load(os.path.join(GOLD, "ref_stepvgg_b2_32x32.npz"))
+    P, g, d = build("fp32")
+    crit = P.VGGLoss(DEV)
+    crit.load_state_dict(orc.init_vgg_state(126))
+    if graph:                                  # lazy one-time set-up outside the capture
+        P2, g0, d0 = build("fp32")
+        c0 = P.VGGLoss(DEV); c0.load_state_dict(orc.init_vgg_state(126))
+        a, b, c = orc.synthetic_batch(2, 32, 32, 5)
+        P.Pix2PixTrainer(g0, d0, vgg=c0).step(a.to(DEV), b.to(DEV), c.to(DEV))
+    tr = P.Pix2PixTrainer(g, d, vgg=crit, cuda_graph=graph, graph_warmup=0)
+    a, b, c = orc.synthetic_batch(2, 32, 32, 123)
+    out = tr.step(a.to(DEV), b.to(DEV), c.to(DEV))
+    assert relerr(out["fake_b"], torch.from_numpy(gold["fake_b"])) <= 2e-4
+    for nm in ("loss_d", "loss_g_gan", "loss_feat", "loss_tv", "loss_vgg", "loss_g"):
+        assert abs(out[nm].item() - float(gold[nm])) <= 2e-4 * abs(float(gold[nm])), (nm, out[nm].item(), float(gold[nm]))
+    # generator gradients now carry the perceptual term: fingerprints of the reference's .grad tensors
+    worst = 0.0
+    for name, p in g.named_parameters():
+        if name.endswith("conv2d.bias") or p.numel() == 1:
+            continue
+        fp, ref = fingerprint(p.grad.float().cpu()), gold["ggrad." + name]
+        rel = abs(fp[2] - ref[2]) / max(ref[2], 1e-30)            # sum of squares
+        worst = max(worst, rel)
+        assert rel <= 0.1, (name, rel)
+    # and it differs from the iteration without the term (the gradients really flow through the VGG stack)
+    assert abs(out["loss_g"].item() - (out["loss_g_gan"] + out["loss_feat"] + out["loss_tv"]).item()) > 1e-3

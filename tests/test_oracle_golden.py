@@ -223,3 +223,30 @@ def test_checkpoint_files_interchange_with_the_reference(tmp_path):
         assert torch.equal(v, g2.state_dict()[k]), k
     for k, v in c.state_dict().items():
         assert torch.equal(v, c2.state_dict()[k]), k
+
+
+# ---- VGG19 perceptual loss ---------------------------------------------------------------------
+def test_oracle_vgg_loss_matches_reference_golden():
+    """orc.vgg_loss against the vectors produced by the reference's own VGGLoss / Vgg19 classes with the same seeded
+    weights (oracle/make_golden_vgg.py)."""
+    from oracle.make_golden_util import VGG_CASES, fingerprint
+    state = orc.init_vgg_state(126)
+    for name, batch, h, w, seed in VGG_CASES:
+        gold = np.load(os.path.join(GOLD, f"ref_vgg_{name}.npz"))
+        a, b, _ = orc.synthetic_batch(batch, h, w, seed)
+        x = torch.tanh(a * 1.5).requires_grad_(True)
+        loss = orc.vgg_loss(state, x, b)
+        loss.backward()
+        assert abs(loss.item() - float(gold["loss"])) <= 1e-5 * abs(float(gold["loss"]))
+        assert np.abs(x.grad.numpy() - gold["grad_x"]).max() <= 1e-4 * np.abs(gold["grad_x"]).max()
+        for i, t in enumerate(orc.vgg_features(state, x.detach())):
+            assert np.allclose(fingerprint(t), gold[f"tap{i}"], rtol=1e-4, atol=1e-5), (name, i)
+
+
+def test_oracle_step_with_vgg_matches_reference_golden():
+    gold = np.load(os.path.join(GOLD, "ref_stepvgg_b2_32x32.npz"))
+    ot = orc.OracleVGGTrainer(orc.init_g_state(123), orc.init_d_state(124), orc.init_vgg_state(126))
+    out = ot.step(*orc.synthetic_batch(2, 32, 32, 123))
+    assert np.abs(out["fake_b"].numpy() - gold["fake_b"]).max() <= 1e-4
+    for nm in ("loss_d", "loss_g_gan", "loss_feat", "loss_tv", "loss_vgg", "loss_g"):
+        assert abs(out[nm].item() - float(gold[nm])) <= 1e-4 * abs(float(gold[nm])), nm
