@@ -30,6 +30,7 @@ import torch  # noqa: E402
 RES_CONV_DRAM_BYTES = 18.19e6      # dram__bytes_read.sum + dram__bytes_write.sum of one residual-conv launch (profiles/r01d_ncu_res_fwd.md)
 FLOP_PER_IMG_256 = 173.41e9          # necessary conv FLOPs of one training step per image
 G_FWD_FLOP_PER_IMG_256 = 32.879e9    # generator forward alone
+VGG_FLOP_PER_IMG_256 = 3 * 47.34e9   # --with-vgg: vgg19.features[0:30] forward on fake_b and real_b + data-gradient for fake_b
 
 
 def load_peaks():
@@ -90,16 +91,27 @@ class ReferenceStep:
     """The reference's iteration on the host cores: its own modules when oracle/_ref/networks.py is present
     (kind "reference"), else the oracle's restatement (kind "port")."""
 
-    def __init__(self, size, batch):
+    def __init__(self, size, batch, with_vgg=False):
         from oracle import pix2pix_oracle as orc
         from oracle.build_ref import load_reference_networks
         import contextlib
         self.orc, self.size, self.batch = orc, size, batch
         ref = load_reference_networks()
         self.kind = "reference" if ref is not None else "port"
+        self.crit_vgg = None
         if ref is None:
-            self.tr = orc.OracleTrainer(orc.init_g_state(123), orc.init_d_state(124))
+            self.tr = (orc.OracleVGGTrainer(orc.init_g_state(123), orc.init_d_state(124), orc.init_vgg_state(126))
+                       if with_vgg else orc.OracleTrainer(orc.init_g_state(123), orc.init_d_state(124)))
             return
+        if with_vgg:
+            # criterionVGG = VGGLoss(device) (train.py:193).  Its constructor downloads the ImageNet weights
+            # (networks.py:35); offline the same architecture is built with torchvision's random initialisation
+            stock = ref.models.vgg19
+            ref.models.vgg19 = lambda pretrained=True, **kw: stock(weights=None)
+            try:
+                self.crit_vgg = ref.VGGLoss("cpu")
+            finally:
+                ref.models.vgg19 = stock
         torch.manual_seed(123)
         with contextlib.redirect_stdout(sys.stderr):
             self.net_g = ref.define_G("normal", 0.02, gpu_id="cpu")
@@ -131,6 +143,8 @@ class ReferenceStep:
         for i in range(3):                                                                # :344-351
             for j in range(len(pred_fake[i]) - 1):
                 loss_g = loss_g + (1.0 / 3) * (4.0 / 4) * self.crit_feat(pred_fake[i][j], pred_real[i][j].detach()) * 10.0
+        if self.crit_vgg is not None:
+            loss_g = loss_g + self.crit_vgg(fake_b, real_b) * 10.0                        # :377
         loss_g = loss_g + torch.mean(torch.abs(fake_b[:, :, :, :-1] - fake_b[:, :, :, 1:])) \
             + torch.mean(torch.abs(fake_b[:, :, :-1, :] - fake_b[:, :, 1:, :]))            # :123-126, :378-380
         self.opt_g.zero_grad(); loss_g.backward(); self.opt_g.step()                      # :384-386
@@ -154,7 +168,7 @@ def run_reference(args, rank, world):
     torch.set_num_threads(cores)
     S, B = args.size, args.batch
     from oracle import pix2pix_oracle as orc
-    ref = ReferenceStep(S, B)
+    ref = ReferenceStep(S, B, args.with_vgg)
     batches = [orc.synthetic_batch(B, S, S, 500 + i) for i in range(2)]
     fn = (lambda bt: ref.infer(bt[2])) if args.mode == "infer" else (lambda bt: ref.step(*bt))
     for i in range(args.warmup):
@@ -266,7 +280,10 @@ def run_ours(args, rank, world, local_rank):
         g = P.define_G("normal", 0.02, gpu_id=dev)
         d = P.define_D(6, 64, gpu_id=dev)
     g.train(); d.train()
-    tr = P.Pix2PixTrainer(g, d, cuda_graph=not args.no_graph)
+    vgg = None
+    if args.with_vgg:                                        # random-init weights of the vgg19 architecture (no download)
+        vgg = P.VGGLoss(dev)
+    tr = P.Pix2PixTrainer(g, d, cuda_graph=not args.no_graph, vgg=vgg)
     tr.broadcast_parameters(0)
 
     # synthetic pairs generated on the device as 8-bit images (what dataset.py decodes from disk); the iteration turns
@@ -428,7 +445,8 @@ def run_ours(args, rank, world, local_rank):
     if rank != 0:
         return
     hbm, tf_burst, tf_sust, which = load_peaks()
-    flop_img = (G_FWD_FLOP_PER_IMG_256 if infer else FLOP_PER_IMG_256) * (S / 256.0) ** 2
+    flop_img = (G_FWD_FLOP_PER_IMG_256 if infer else FLOP_PER_IMG_256 + (VGG_FLOP_PER_IMG_256 if args.with_vgg else 0.0)) \
+        * (S / 256.0) ** 2
     line = {"metric": metric_name(args), "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16" if args.precision.startswith("bf16") else "f32", "data": "synthetic",
@@ -446,6 +464,7 @@ def run_ours(args, rank, world, local_rank):
                     "no_prefetch": {"value": e2e_serial, "ms_per_step": ms_serial},
                     "h2d_probe_gbs": probe_gbs},
             "gpu_launches": launches,
+            "flop_per_image": flop_img,
             "step_tensor_frac": value / world * flop_img / (tf_sust * 1e12)}
     if not infer:
         line["final_losses"] = {"loss_d": out["loss_d"].item(), "loss_g": out["loss_g"].item()}
@@ -467,7 +486,7 @@ def run_ours(args, rank, world, local_rank):
         from oracle import pix2pix_oracle as orc
         cores = os.cpu_count() or 1
         torch.set_num_threads(cores)
-        ref = ReferenceStep(S, B)
+        ref = ReferenceStep(S, B, args.with_vgg)
         ob = orc.synthetic_batch(B, S, S, 77)
         fn = (lambda: ref.infer(ob[2])) if infer else (lambda: ref.step(*ob))
         fn()

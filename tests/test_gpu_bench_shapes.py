@@ -78,8 +78,16 @@ def E_d_layers():
     return [(6, 64, 2, False), (64, 128, 2, True), (128, 256, 2, True), (256, 512, 1, True), (512, 1, 1, False)]
 
 
+def vgg_cases(B, S, tag):
+    """the thirteen 3x3 pad-1 convolutions of vgg19.features[0:30] on the 2B images of cat(fake_b, real_b)
+    (engine.VGGLossFunction): distinct shapes only"""
+    return [(f"{tag}.vgg.c{cin}_{cout}_{h}", 2 * B, cin, cout, h, 3, 1, 1)
+            for cin, cout, h in ((3, 64, S), (64, 64, S), (64, 128, S // 2), (128, 128, S // 2), (128, 256, S // 4),
+                                 (256, 256, S // 4), (256, 512, S // 8), (512, 512, S // 8), (512, 512, S // 16))]
+
+
 CASES = layer_cases(16, 256, "b16s256") + layer_cases(4, 512, "b4s512") + \
-    [c for c in layer_cases(64, 256, "b64s256") if ".g." in c[0]]
+    [c for c in layer_cases(64, 256, "b64s256") if ".g." in c[0]] + vgg_cases(16, 256, "b16s256")
 
 
 @pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
@@ -93,14 +101,15 @@ def test_conv_at_bench_shape(case):
     Ci, Co = E.pad16(cin), E.pad16(cout)
     xs = to_stored(x, Ci, dt)
     del x
-    plan = E.ConvPlan(B, H, H, Ci, cin, cout, k, s, pad)
+    relu = ".vgg." in name                     # the VGG stack applies ReLU in the convolution's epilogue
+    plan = E.ConvPlan(B, H, H, Ci, cin, cout, k, s, pad, L.ACT_RELU if relu else L.ACT_NONE)
     P.set_precision("bf16")
     L.trace_begin()
     try:
         plan.pack(w, None, dt)
         out = torch.empty(B, plan.Ho, plan.Wo, Co, dtype=dt, device=DEV)
         stats = torch.zeros(2 * Co, dtype=torch.float64, device=DEV)
-        plan.fwd(xs, bias, out, stats)
+        plan.fwd(xs, bias, out, None if relu else stats)      # (statistics are taken before any activation)
         out2 = torch.full_like(out, 3.0)
         plan.fwd(xs, bias, out2, None)          # the discriminator's call (one-channel layers: 1x1 + tap gather)
         torch.manual_seed(zlib.crc32(name.encode()) % 1000)
@@ -116,15 +125,17 @@ def test_conv_at_bench_shape(case):
     # reference: torch fp32 (TF32 off) on the same rounded operands
     xr = from_stored(xs, cin).requires_grad_(True)
     wr = w.to(dt).float().requires_grad_(True)
-    ref = F.conv2d(xr, wr, bias, stride=s, padding=pad)
+    pre = F.conv2d(xr, wr, bias, stride=s, padding=pad)
+    ref = F.relu(pre) if relu else pre
     got = from_stored(out, cout)
     assert relerr(got, ref) <= 1e-2, f"{name} fwd {relerr(got, ref):.3e}"
     if Co > cout:
         assert out[..., cout:].abs().max().item() == 0
-    st_ref = torch.stack([got.double().sum((0, 2, 3)), (got.double() ** 2).sum((0, 2, 3))])
-    assert relerr(stats.view(2, Co)[:, :cout], st_ref) <= 1e-6, f"{name} stats"     # sums of what was stored, in fp64
+    if not relu:
+        st_ref = torch.stack([got.double().sum((0, 2, 3)), (got.double() ** 2).sum((0, 2, 3))])
+        assert relerr(stats.view(2, Co)[:, :cout], st_ref) <= 1e-6, f"{name} stats"     # sums of what was stored, in fp64
     assert relerr(from_stored(out2, cout), ref) <= 1e-2, f"{name} fwd without stats"
-    ref.backward(from_stored(gos, cout))
+    pre.backward(from_stored(gos, cout))       # dgrad / wgrad take the gradient w.r.t. the convolution's own output
     assert relerr(from_stored(din, cin), xr.grad) <= 1e-2, f"{name} dgrad {relerr(from_stored(din, cin), xr.grad):.3e}"
     if Ci > cin:
         assert din[..., cin:].abs().max().item() == 0
