@@ -528,6 +528,8 @@ def main():
     if world > 1:
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        # (capping NCCL's CTAs was measured at N=2 and does not pay: 2 / 4 / 8 / 32 CTAs -> 10.49 / 10.35 / 10.18 /
+        # 10.14 ms per step, profiles/r02f_scale2b.txt; NCCL's own choice stays)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     try:
         run_ours(args, rank, world, local_rank)

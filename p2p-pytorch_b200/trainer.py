@@ -76,7 +76,13 @@ class Pix2PixTrainer:
         self.red_g = GradReducer(process_group, bucket_bytes)
         self.red_d = GradReducer(process_group, bucket_bytes)
         self.world = self.red_g.world
-        # overlap=False: both all-reduces start after both backward passes (nothing competes for SMs)
+        # overlap=True (default): D's all-reduce starts right after loss_d.backward() and travels while G's backward runs;
+        # P2P_DP_OVERLAP=0 starts both all-reduces after both backward passes.  Measured (ms/step, N=1 / N=2 / N=8):
+        # one 8-GPU box overlapped 9.73 / 10.08 / 10.21 (profiles/r01e_bench_N*.json), not overlapped 9.75 / 10.17 /
+        # 10.31 (profiles/r02g_bench_N*.json); a 2-GPU box overlapped 9.83 / 10.13, not overlapped 9.83 / 9.95
+        # (profiles/r02f_scale2c.txt).  Overlapping hides the transfer, but NCCL's CTAs take SMs from the persistent
+        # one-CTA-per-SM convolution kernels, whose 148-CTA grids then need a second wave; which effect wins depends on
+        # the box, and the 8-GPU boxes favour overlapping.
         self.overlap = os.environ.get("P2P_DP_OVERLAP", "1") != "0"
         self.optimizer_g.grad_scale = self.optimizer_d.grad_scale = 1.0 / self.world
         self._c_reals = [c[1] for c in net_d._cfg]
