@@ -466,8 +466,11 @@ class DiscriminatorFunction(torch.autograd.Function):
         sn_idx = [(sc, j) for sc in range(NUM_D) for j in range(nl) if layer_cfg[j][3]]
         sig_of = {}
         if sn_idx:
-            wbars = [params[2 * (sc * nl + j)].detach() for sc, j in sn_idx]
-            sigma_all = spectral_power_iteration(wbars, [u for u, _ in sn_bufs], [v for _, v in sn_bufs])
+            sigma_all = aux.get("sigma")
+            if sigma_all is None:
+                wbars = [params[2 * (sc * nl + j)].detach() for sc, j in sn_idx]
+                sigma_all = spectral_power_iteration(wbars, [u for u, _ in sn_bufs], [v for _, v in sn_bufs])
+            # (else: the caller ran this pass's power iteration ahead of time, MultiscaleDiscriminator.power_iteration)
             sig_of = {key: sigma_all[i:i + 1] for i, key in enumerate(sn_idx)}
         # A second pass over the SAME pair within one iteration (train.py:308 and :336 both see (real_a, fake_b)) may
         # reuse the input pyramid and the first layer's outputs of the first one: that layer has no spectral norm, so

@@ -249,7 +249,18 @@ class MultiscaleDiscriminator(nn.Module):
             params = [p.detach() for p in params]
         return params, refs, sn_bufs
 
-    def forward_stored(self, a, b=None, frozen=False, first_layer_cache=None):
+    def power_iteration(self):
+        """One power iteration of every spectral-norm layer (what each forward pass starts with, networks.py:537-547):
+        advances u, v in place and returns the nine sigmas.  u, v depend only on the weights and on their own previous
+        value, so a caller that runs several passes between two optimizer steps may run their power iterations first,
+        in order, and hand each pass its `sigma` -- the passes themselves then no longer depend on one another."""
+        params, _refs, sn_bufs = self._gather(True)
+        nl = len(self._cfg)
+        sn_idx = [(sc, j) for sc in range(self.num_D) for j in range(nl) if self._cfg[j][3]]
+        wbars = [params[2 * (sc * nl + j)] for sc, j in sn_idx]
+        return E.spectral_power_iteration(wbars, [u for u, _ in sn_bufs], [v for _, v in sn_bufs])
+
+    def forward_stored(self, a, b=None, frozen=False, first_layer_cache=None, sigma=None):
         """15 stored maps (scale-major, full resolution first).  `frozen=True` treats the weights as constants:
         gradients still reach the input, no weight gradients are computed (what `loss_g.backward()` needs;
         the reference computes and then discards them, train.py:385-388).
@@ -257,7 +268,8 @@ class MultiscaleDiscriminator(nn.Module):
         caller's promise): the first pass fills it, the second reuses the input pyramid and the outputs of the first
         layer (no spectral norm there, so they are bit-identical) instead of recomputing them."""
         params, refs, sn_bufs = self._gather(frozen)
-        aux = dict(layer_cfg=self._cfg, sn_bufs=sn_bufs, param_refs=refs, first_layer_cache=first_layer_cache)
+        aux = dict(layer_cfg=self._cfg, sn_bufs=sn_bufs, param_refs=refs, first_layer_cache=first_layer_cache,
+                   sigma=sigma)
         outs = E.DiscriminatorFunction.apply(a, b, aux, *params)
         nl = len(self._cfg)
         return [list(outs[i * nl:(i + 1) * nl]) for i in range(self.num_D)]

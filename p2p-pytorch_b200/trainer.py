@@ -54,7 +54,8 @@ class Pix2PixTrainer:
     """optimizer_g / optimizer_d loop of train.py:241-242, :294-390."""
 
     def __init__(self, net_g, net_d, lr: float = 2e-4, beta1: float = 0.5, process_group=None,
-                 bucket_bytes: int = 64 << 20, cuda_graph: bool = False, graph_warmup: int = 2, net_c=None, vgg=None):
+                 bucket_bytes: int = 64 << 20, cuda_graph: bool = False, graph_warmup: int = 2, net_c=None, vgg=None,
+                 two_lanes: Optional[bool] = None):
         self.net_g, self.net_d, self.net_c = net_g, net_d, net_c
         # vgg: a VGGLoss module (criterionVGG, train.py:193) -- adds content_loss = vgg(fake_b, real_b) * 10 to loss_g
         # (train.py:377-380) and, in step_full, c_percp = vgg(compressed, real_b) * 10 to the logged phase-3 loss (:395)
@@ -86,6 +87,13 @@ class Pix2PixTrainer:
         self.overlap = os.environ.get("P2P_DP_OVERLAP", "1") != "0"
         self.optimizer_g.grad_scale = self.optimizer_d.grad_scale = 1.0 / self.world
         self._c_reals = [c[1] for c in net_d._cfg]
+        # two_lanes: the discriminator's own training (passes 1-2, loss_d, its backward, Adam D) runs on a second CUDA
+        # stream beside the generator's (G forward, pass 3, loss_g, its backward, Adam G); see _step_two_lanes.
+        # Default: on whenever the iteration is replayed from a CUDA graph (kernel-by-kernel launching is host-bound,
+        # a second stream gains nothing there).  P2P_LANES=1 / 2 overrides.
+        env_lanes = os.environ.get("P2P_LANES")
+        self.two_lanes = (self.cuda_graph if two_lanes is None else bool(two_lanes)) if env_lanes is None else env_lanes == "2"
+        self._side = None
         if self.cuda_graph:
             self.optimizer_g.make_capturable()
             self.optimizer_d.make_capturable()
@@ -261,7 +269,78 @@ class Pix2PixTrainer:
         self.graph_launches = L.launch_count() - before
         return {"graph": graph, "inputs": inputs, "outputs": outputs}
 
+    def _step_two_lanes(self, real_a, real_b, g_input):
+        """The same iteration on two CUDA streams.  The discriminator's training and the generator's are two chains of
+        kernels that meet in three places only: D's passes over the fake pair need fake_b, the feature-matching loss
+        needs pass 2's maps, and Adam may move D's weights only once pass 3 has read them.  Each chain alone leaves SMs
+        idle (second waves of the persistent convolution kernels, small maps of the coarse D scales, memory-bound
+        elementwise kernels); side by side they fill each other's gaps.
+
+        Exactness: the three power iterations of the spectral-norm layers depend only on the weights and on their own
+        previous u, v, so they run first, in the reference's order, and each pass gets its sigma; everything else is
+        the eager order with independent work moved to the second stream (the first-layer sharing between passes 1
+        and 3 is dropped: they now run at the same time)."""
+        net_g, net_d, cr = self.net_g, self.net_d, self._c_reals
+        last = lambda maps: [s[-1] for s in maps]                                         # noqa: E731
+        ones = [1] * 3
+        main = torch.cuda.current_stream()
+        if self._side is None:
+            self._side = torch.cuda.Stream(device=real_a.device)
+        side = self._side
+        sig1, sig2, sig3 = (net_d.power_iteration() for _ in range(3))                    # passes 1, 2, 3 (:309, :316, :337)
+        self.optimizer_g.zero_grad()                                                      # :384
+        side.wait_stream(main)
+        with torch.cuda.stream(side):                                                     # ---- D lane ----
+            self.optimizer_d.zero_grad()                                                  # :388
+            pred_real = net_d.forward_stored(real_a, real_b, sigma=sig2)                  # :315-316
+            loss_d_real = lsgan_loss(last(pred_real), ones, 1.0)                          # :317
+            ev_real = torch.cuda.Event()
+            ev_real.record(side)
+        fake_b = net_g(g_input)                                                           # :300 (beside pass 2)
+        ev_fake = torch.cuda.Event()
+        ev_fake.record(main)
+        with torch.cuda.stream(side):
+            side.wait_event(ev_fake)
+            fake_b.record_stream(side)
+            pred_fake_d = net_d.forward_stored(real_a, fake_b.detach(), sigma=sig1)       # :308-309
+            loss_d_fake = lsgan_loss(last(pred_fake_d), ones, 0.0)                        # :310
+            loss_d = (loss_d_fake + loss_d_real) * 0.5                                    # :320
+        # ---- G lane ----
+        pred_fake = net_d.forward_stored(real_a, fake_b, frozen=True, sigma=sig3)         # :336-337
+        ev_pass3 = torch.cuda.Event()
+        ev_pass3.record(main)                              # D's weights have been read (packed) for the last time
+        loss_g_gan = lsgan_loss(last(pred_fake), ones, 1.0)                               # :338
+        main.wait_event(ev_real)
+        for s in pred_real:
+            for t in s:
+                t.record_stream(main)
+        loss_feat = feature_matching_loss(pred_fake, pred_real, cr)                       # :344-351
+        loss_tv = tv_loss(fake_b)                                                         # :378
+        loss_g = loss_g_gan + loss_feat + loss_tv                                         # :353,:380
+        loss_vgg = None
+        if self.vgg is not None:
+            loss_vgg = self.vgg(fake_b, real_b) * 10.0                                    # :377
+            loss_g = loss_g + loss_vgg
+        with torch.cuda.stream(side):
+            loss_d.backward()                                                             # :389
+            self.red_d.launch(self.optimizer_d.flat_g)
+            side.wait_event(ev_pass3)
+            self.red_d.wait()
+            self.optimizer_d.step()                                                       # :390
+        loss_g.backward()                                                                 # :385
+        self.red_g.launch(self.optimizer_g.flat_g)
+        self.red_g.wait()
+        self.optimizer_g.step()                                                           # :386
+        main.wait_stream(side)
+        out = {"fake_b": fake_b.detach(), "loss_d": loss_d.detach(), "loss_g_gan": loss_g_gan.detach(),
+               "loss_feat": loss_feat.detach(), "loss_tv": loss_tv.detach(), "loss_g": loss_g.detach()}
+        if loss_vgg is not None:
+            out["loss_vgg"] = loss_vgg.detach()
+        return out
+
     def _step_eager(self, real_a: torch.Tensor, real_b: torch.Tensor, g_input: torch.Tensor) -> Dict[str, torch.Tensor]:
+        if self.two_lanes:
+            return self._step_two_lanes(real_a, real_b, g_input)
         net_g, net_d, cr = self.net_g, self.net_d, self._c_reals
         last = lambda maps: [s[-1] for s in maps]                                         # noqa: E731
         ones = [1] * 3

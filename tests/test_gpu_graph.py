@@ -209,3 +209,34 @@ def test_uint8_batches_equal_float_batches(graph):
     for x, y in zip(rec["float"], rec["u8"]):
         for u, v in zip(x, y):
             assert abs(u - v) <= 1e-3 * abs(u), (rec["float"], rec["u8"])
+
+
+@pytest.mark.parametrize("precision,tol", [("fp32", 1e-5), ("bf16", 1e-2)])
+def test_two_stream_iteration_equals_single_stream(precision, tol):
+    """Pix2PixTrainer(two_lanes=True) -- D's training on a second CUDA stream, its three power iterations hoisted to the
+    front -- against the single-stream order of the reference, kernel by kernel launched, from the same state on the
+    same batches: outputs, gradients and spectral-norm vectors agree to the run-to-run noise of the float atomics."""
+    import p2p_pytorch_b200 as P
+    P.set_precision(precision)
+    g1, d1 = _nets(P)
+    g2, d2 = _nets(P)
+    tr2 = P.Pix2PixTrainer(g1, d1, two_lanes=True)
+    tr1 = P.Pix2PixTrainer(g2, d2, two_lanes=False)
+    assert tr2.two_lanes and not tr1.two_lanes
+    for it in range(4):
+        g2.load_state_dict(g1.state_dict())
+        d2.load_state_dict(d1.state_dict())
+        tr1.optimizer_g.load_state_dict(tr2.optimizer_g.state_dict())
+        tr1.optimizer_d.load_state_dict(tr2.optimizer_d.state_dict())
+        batch = [t.to(DEV) for t in orc.synthetic_batch(2, 32, 32, 150 + it)]
+        o2 = {k: v.detach().float().clone() for k, v in tr2.step(*batch).items()}
+        o1 = {k: v.detach().float() for k, v in tr1.step(*batch).items()}
+        torch.cuda.synchronize()
+        for k in ("loss_d", "loss_g", "loss_feat", "loss_tv", "loss_g_gan"):
+            assert abs(o2[k].item() - o1[k].item()) <= tol * abs(o1[k].item()), (it, k, o2[k].item(), o1[k].item())
+        assert (o2["fake_b"] - o1["fake_b"]).abs().max().item() <= tol, it
+        for oa, ob in ((tr2.optimizer_g, tr1.optimizer_g), (tr2.optimizer_d, tr1.optimizer_d)):
+            assert _rms_rel(oa.flat_g, ob.flat_g) <= (1e-3 if precision == "fp32" else 5e-2), (it, _rms_rel(oa.flat_g, ob.flat_g))
+        for (n, b1), (_, b2) in zip(d1.named_parameters(), d2.named_parameters()):
+            if n.endswith(("weight_u", "weight_v")):
+                assert torch.allclose(b1, b2, rtol=1e-5, atol=1e-7), (it, n)
