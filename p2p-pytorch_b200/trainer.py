@@ -93,7 +93,7 @@ class Pix2PixTrainer:
         # a second stream gains nothing there).  P2P_LANES=1 / 2 overrides.
         env_lanes = os.environ.get("P2P_LANES")
         self.two_lanes = (self.cuda_graph if two_lanes is None else bool(two_lanes)) if env_lanes is None else env_lanes == "2"
-        self._side = None
+        self._side = self._side_vgg = None
         if self.cuda_graph:
             self.optimizer_g.make_capturable()
             self.optimizer_d.make_capturable()
@@ -305,6 +305,14 @@ class Pix2PixTrainer:
             pred_fake_d = net_d.forward_stored(real_a, fake_b.detach(), sigma=sig1)       # :308-309
             loss_d_fake = lsgan_loss(last(pred_fake_d), ones, 0.0)                        # :310
             loss_d = (loss_d_fake + loss_d_real) * 0.5                                    # :320
+        loss_vgg = None
+        if self.vgg is not None:                           # ---- perceptual lane: beside pass 3 (its backward too) ----
+            if self._side_vgg is None:
+                self._side_vgg = torch.cuda.Stream(device=real_a.device)
+            with torch.cuda.stream(self._side_vgg):
+                self._side_vgg.wait_event(ev_fake)
+                fake_b.record_stream(self._side_vgg)
+                loss_vgg = self.vgg(fake_b, real_b) * 10.0                                # :377
         # ---- G lane ----
         pred_fake = net_d.forward_stored(real_a, fake_b, frozen=True, sigma=sig3)         # :336-337
         ev_pass3 = torch.cuda.Event()
@@ -317,9 +325,8 @@ class Pix2PixTrainer:
         loss_feat = feature_matching_loss(pred_fake, pred_real, cr)                       # :344-351
         loss_tv = tv_loss(fake_b)                                                         # :378
         loss_g = loss_g_gan + loss_feat + loss_tv                                         # :353,:380
-        loss_vgg = None
-        if self.vgg is not None:
-            loss_vgg = self.vgg(fake_b, real_b) * 10.0                                    # :377
+        if loss_vgg is not None:
+            main.wait_stream(self._side_vgg)
             loss_g = loss_g + loss_vgg
         with torch.cuda.stream(side):
             loss_d.backward()                                                             # :389
