@@ -283,10 +283,26 @@ class Pix2PixTrainer:
         net_g, net_d, cr = self.net_g, self.net_d, self._c_reals
         last = lambda maps: [s[-1] for s in maps]                                         # noqa: E731
         ones = [1] * 3
-        main = torch.cuda.current_stream()
+        outer = torch.cuda.current_stream()
         if self._side is None:
             self._side = torch.cuda.Stream(device=real_a.device)
-        side = self._side
+            # the generator's chain is the longer one: it runs on a HIGH-priority stream, so that whenever CTAs of both
+            # chains are waiting for SMs the critical path goes first (P2P_G_PRIORITY=0: same priority)
+            prio = -1 if os.environ.get("P2P_G_PRIORITY", "1") != "0" else 0
+            self._g_lane = torch.cuda.Stream(device=real_a.device, priority=prio)
+        side, main = self._side, self._g_lane
+        main.wait_stream(outer)
+        with torch.cuda.stream(main):
+            out = self._two_lanes_body(real_a, real_b, g_input, main, side)
+        outer.wait_stream(main)
+        for t in out.values():
+            t.record_stream(outer)
+        return out
+
+    def _two_lanes_body(self, real_a, real_b, g_input, main, side):
+        net_g, net_d, cr = self.net_g, self.net_d, self._c_reals
+        last = lambda maps: [s[-1] for s in maps]                                         # noqa: E731
+        ones = [1] * 3
         sig1, sig2, sig3 = (net_d.power_iteration() for _ in range(3))                    # passes 1, 2, 3 (:309, :316, :337)
         self.optimizer_g.zero_grad()                                                      # :384
         side.wait_stream(main)
