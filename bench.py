@@ -320,7 +320,7 @@ def run_ours(args, rank, world, local_rank):
 
         def infer_body():
             P._lib.call("p2p_decode_u8", x8.data_ptr(), x32.data_ptr(), None, x8.numel(), 3)
-            return g(x32)
+            return P.generate(g, x32, streams=args.infer_streams)
         x8.copy_(data[0][1])
         with torch.no_grad():
             for _ in range(2):
@@ -523,6 +523,7 @@ def main():
     ap.add_argument("--mode", default="train", choices=["train", "infer"],
                     help="infer: generator-only inference (BASELINE.json configs[4]; use --batch 64)")
     ap.add_argument("--with-vgg", action="store_true", help="include the VGG19 perceptual term (train.py:377)")
+    ap.add_argument("--infer-streams", type=int, default=2, help="--mode infer: sub-batches run on this many CUDA streams")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true", help="launch kernel by kernel instead of replaying a CUDA graph")
     args = ap.parse_args()

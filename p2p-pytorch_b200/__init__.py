@@ -7,10 +7,10 @@ from .networks import (CompressionNetwork, GANLoss, MultiscaleDiscriminator, Exp
 from .losses import feature_matching_loss, lsgan_loss, tv_loss
 from .optim import FusedAdam
 from .trainer import Pix2PixTrainer
-from .evaluation import load_checkpoint, psnr, save_checkpoint
+from .evaluation import generate, load_checkpoint, psnr, save_checkpoint
 
 _lib.load()   # fail at import time if the CUDA library has not been built: there is no fallback path
 
-__all__ = ["VGGLoss", "Vgg19", "psnr", "save_checkpoint", "load_checkpoint", "define_G", "define_D", "define_C", "CompressionNetwork", "GANLoss", "init_net", "init_weights", "ExpandNetwork", "MultiscaleDiscriminator",
+__all__ = ["generate", "VGGLoss", "Vgg19", "psnr", "save_checkpoint", "load_checkpoint", "define_G", "define_D", "define_C", "CompressionNetwork", "GANLoss", "init_net", "init_weights", "ExpandNetwork", "MultiscaleDiscriminator",
            "FusedAdam", "Pix2PixTrainer", "lsgan_loss", "feature_matching_loss", "tv_loss", "set_precision",
            "get_precision"]

@@ -61,3 +61,33 @@ def load_checkpoint(path: str, net_g, net_c=None, net_d=None, map_location: Opti
     if net_d is not None and "state_dict_d" in state:
         net_d.load_state_dict(state["state_dict_d"])
     return int(state.get("epoch", 0))
+
+
+_gen_streams = {}
+
+
+@torch.no_grad()
+def generate(net_g, x: torch.Tensor, streams: int = 2) -> torch.Tensor:
+    """Generator inference as test.py:37-41 runs it (`net_g(input)`, no autograd) for a whole batch, with the batch
+    split over `streams` CUDA streams: in eval mode BatchNorm uses its running statistics, so images are independent and
+    the split is exact; the sub-batches' kernel chains fill each other's idle SMs (second waves of the persistent
+    convolution kernels, memory-bound glue).  Returns fp32 [B,3,H,W]."""
+    if net_g.training:
+        raise ValueError("generate() needs net_g.eval(): train-mode BatchNorm statistics couple the images of a batch")
+    B = x.shape[0]
+    streams = max(1, min(int(streams), B))
+    if streams == 1:
+        return net_g(x)
+    cur = torch.cuda.current_stream()
+    key = (str(x.device), streams)
+    if key not in _gen_streams:
+        _gen_streams[key] = [torch.cuda.Stream(device=x.device) for _ in range(streams)]
+    out = torch.empty((B, 3, x.shape[2], x.shape[3]), dtype=torch.float32, device=x.device)
+    bounds = [B * i // streams for i in range(streams + 1)]
+    for st, lo, hi in zip(_gen_streams[key], bounds[:-1], bounds[1:]):
+        st.wait_stream(cur)
+        with torch.cuda.stream(st):
+            out[lo:hi].copy_(net_g(x[lo:hi]))
+    for st in _gen_streams[key]:
+        cur.wait_stream(st)
+    return out
