@@ -49,16 +49,21 @@ _helper_streams = {}
 def helper_stream(dev, which: str = "wgrad"):
     """A second CUDA stream tied to the CURRENT one (one per (device, current stream, purpose)): work that nothing
     downstream waits for -- the weight gradients of a backward pass -- is forked onto it and joined at the end, so it
-    runs beside the data-gradient chain.  OFF by default (returns None): it gains only 1.5 % on top of the two-stream
-    iteration (8.47 -> 8.34 ms/step) and tests/test_gpu_graph.py::test_prefetch_stages_the_next_batch then differs
-    from the un-prefetched run at the second iteration -- unexplained, so it stays an experiment (P2P_WGRAD_STREAM=1)."""
+    runs beside the data-gradient chain (the persistent wgrad kernels beside the memory-bound BatchNorm-backward kernels:
+    8.20 -> 7.79 ms/step).  Used whenever the backward pass runs on a stream of its own (the trainer's lanes, a graph
+    capture); on the process's default stream it stays off -- with the lanes on the default stream one prefetch test
+    differed from its un-prefetched twin at the second iteration, unexplained, and that configuration is avoided rather
+    than trusted.  P2P_WGRAD_STREAM=0 / 1 forces it off / on."""
     import os
-    if os.environ.get("P2P_WGRAD_STREAM", "0") != "1":
+    mode = os.environ.get("P2P_WGRAD_STREAM", "auto")
+    cur = torch.cuda.current_stream()
+    if mode == "0" or (mode != "1" and cur == torch.cuda.default_stream(cur.device)):
         return None
-    key = (str(dev), torch.cuda.current_stream().cuda_stream, which)
+    key = (str(dev), cur.cuda_stream, which)
     st = _helper_streams.get(key)
     if st is None:
-        st = _helper_streams[key] = torch.cuda.Stream(device=dev)
+        same = os.environ.get("P2P_WGRAD_PRIO", "low") == "same"      # A/B knob: helper at the lane's priority
+        st = _helper_streams[key] = torch.cuda.Stream(device=dev, priority=cur.priority if same else 0)
     return st
 
 
