@@ -46,7 +46,7 @@ def get_precision() -> str:
 _helper_streams = {}
 
 
-def helper_stream(dev, which: str = "wgrad"):
+def helper_stream(dev, which: str = "wgrad", same_priority: bool = False):
     """A second CUDA stream tied to the CURRENT one (one per (device, current stream, purpose)): work that nothing
     downstream waits for -- the weight gradients of a backward pass -- is forked onto it and joined at the end, so it
     runs beside the data-gradient chain (the persistent wgrad kernels beside the memory-bound BatchNorm-backward kernels:
@@ -56,14 +56,17 @@ def helper_stream(dev, which: str = "wgrad"):
     than trusted.  P2P_WGRAD_STREAM=0 / 1 forces it off / on."""
     import os
     mode = os.environ.get("P2P_WGRAD_STREAM", "auto")
+    if which != "wgrad":
+        mode = os.environ.get("P2P_SCALE_STREAMS", "auto")
     cur = torch.cuda.current_stream()
     if mode == "0" or (mode != "1" and cur == torch.cuda.default_stream(cur.device)):
         return None
     key = (str(dev), cur.cuda_stream, which)
     st = _helper_streams.get(key)
     if st is None:
-        same = os.environ.get("P2P_WGRAD_PRIO", "low") == "same"      # A/B knob: helper at the lane's priority
-        st = _helper_streams[key] = torch.cuda.Stream(device=dev, priority=cur.priority if same else 0)
+        # weight gradients: lowest priority (nothing waits for them: 7.99 -> 7.79 ms/step against the lane's priority);
+        # the coarse discriminator scales are part of the lane's chain and keep its priority
+        st = _helper_streams[key] = torch.cuda.Stream(device=dev, priority=cur.priority if same_priority else 0)
     return st
 
 
@@ -542,29 +545,49 @@ class DiscriminatorFunction(torch.autograd.Function):
                 packs[(sc, j)] = pk
                 ci = cout
         L.call_multi("p2p_pack_weights_multi", jobs, dc)
+        # The three scales are independent chains of five convolutions; the two coarse ones (64x64 and 32x32 inputs
+        # at 256x256) are short, latency-bound kernels.  Where this pass runs on a stream of its own they go to two
+        # helper streams of the same priority and run beside the full-resolution scale.
+        lane = torch.cuda.current_stream()
+        scale_streams = [None] + [helper_stream(dev, f"scale{i}", same_priority=True) for i in range(1, NUM_D)]
+        ev_ready = None
+        if any(st is not None for st in scale_streams):
+            ev_ready = torch.cuda.Event()
+            ev_ready.record(lane)
         for i in range(NUM_D):
             sc = NUM_D - 1 - i
             h, w = pyr_shapes[i][1:3]
-            if reuse:
-                cur = cache["inputs"][i]
-            else:
-                cur = _empty((B, h, w, 16), dt, dev)
-                call("p2p_cast_pad_channels", ptr(xs32[i]), ptr(cur), B * h * w, 8, 16, dc)
-            cin_real = ca + cb
-            for j, (_cin, cout, stride, _sn) in enumerate(layer_cfg):
-                wgt, bias = params[2 * (sc * nl + j)], params[2 * (sc * nl + j) + 1]
-                act = L.ACT_LRELU if j != nl - 1 else L.ACT_NONE
-                plan = ConvPlan(B, cur.shape[1], cur.shape[2], cur.shape[3], cin_real, cout, 4, stride, 2, act)
-                plan.wp, plan.wt, plan.w1x1 = packs[(sc, j)].wp, packs[(sc, j)].wt, packs[(sc, j)].w1x1
-                if reuse and j == 0:
-                    o = cache["l0"][i].detach()        # an alias of its own: each Function owns its output objects
+            st = scale_streams[i]
+            if st is not None:
+                st.wait_event(ev_ready)
+            with torch.cuda.stream(st if st is not None else lane):
+                if reuse:
+                    cur = cache["inputs"][i]
                 else:
-                    o = _empty((B, plan.Ho, plan.Wo, plan.Co), dt, dev)
-                    plan.fwd(cur, bias, o, None)
-                plans.append(plan)
-                inputs.append(cur)
-                outs.append(o)
-                cur, cin_real = o, cout
+                    cur = _empty((B, h, w, 16), dt, dev)
+                    call("p2p_cast_pad_channels", ptr(xs32[i]), ptr(cur), B * h * w, 8, 16, dc)
+                    if st is not None:
+                        cur.record_stream(lane)
+                cin_real = ca + cb
+                for j, (_cin, cout, stride, _sn) in enumerate(layer_cfg):
+                    wgt, bias = params[2 * (sc * nl + j)], params[2 * (sc * nl + j) + 1]
+                    act = L.ACT_LRELU if j != nl - 1 else L.ACT_NONE
+                    plan = ConvPlan(B, cur.shape[1], cur.shape[2], cur.shape[3], cin_real, cout, 4, stride, 2, act)
+                    plan.wp, plan.wt, plan.w1x1 = packs[(sc, j)].wp, packs[(sc, j)].wt, packs[(sc, j)].w1x1
+                    if reuse and j == 0:
+                        o = cache["l0"][i].detach()        # an alias of its own: each Function owns its output objects
+                    else:
+                        o = _empty((B, plan.Ho, plan.Wo, plan.Co), dt, dev)
+                        plan.fwd(cur, bias, o, None)
+                        if st is not None:
+                            o.record_stream(lane)
+                    plans.append(plan)
+                    inputs.append(cur)
+                    outs.append(o)
+                    cur, cin_real = o, cout
+        for st in scale_streams:
+            if st is not None:
+                lane.wait_stream(st)
         ctx.set_materialize_grads(False)
         ctx.plans, ctx.inputs, ctx.outs_ref = plans, inputs, outs
         ctx.sig_of, ctx.sn_bufs, ctx.sn_idx = sig_of, sn_bufs, sn_idx
@@ -600,63 +623,81 @@ class DiscriminatorFunction(torch.autograd.Function):
             acc_slab = _zeros((off + len(sn_pos),), torch.float32, dev)   # + one dot product per spectral-norm layer
             dots = acc_slab[off:]
         unpack_jobs, sn_jobs = [], []
-        cur_stream = torch.cuda.current_stream()
-        ws = helper_stream(dev) if any(need_w) else None
+        lane = torch.cuda.current_stream()
+        # as in forward: the coarse scales run on helper streams beside the full-resolution one
+        scale_streams = [None] + [helper_stream(dev, f"scale{i}", same_priority=True) for i in range(1, NUM_D)]
+        ev_ready = None
+        if any(st is not None for st in scale_streams):
+            ev_ready = torch.cuda.Event()
+            ev_ready.record(lane)           # incoming gradients and the zeroed accumulators are ready
         dx32 = [None] * NUM_D       # fp32 gradient of each pyramid level (only when need_b)
         for i in reversed(range(NUM_D)):
             sc = NUM_D - 1 - i
-            g_next = None           # gradient arriving from the layer above (its dgrad output)
-            for j in reversed(range(nl)):
-                idx = i * nl + j
-                plan, x_in, o = plans[idx], inputs[idx], outs[idx]
-                gu = gouts[idx]
-                if gu is not None:
-                    if gu.dtype != dt or tuple(gu.shape) != tuple(o.shape):
-                        raise L.P2PError("gradient of a discriminator map must have the map's stored layout")
-                    gu = gu.contiguous()
-                if gu is None and g_next is None:
-                    continue        # nothing has reached this layer yet
-                k = sc * nl + j
-                cout = layer_cfg[j][1]
-                dz = _empty(tuple(o.shape), dt, dev)
-                gbias = None
-                if need_bias[k]:
-                    gbias, ret[2 * k + 1] = _grad_slot(refs[2 * k + 1])
-                call("p2p_act_bwd", ptr(o), ptr(gu), ptr(g_next), ptr(dz), ptr(gbias), B * plan.Ho * plan.Wo, plan.Co,
-                     cout, plan.act, dc)
-                if need_w[k]:
-                    pw = refs[2 * k]
-                    gw, ret[2 * k] = _grad_slot(pw)
-                    acc = acc_slab[acc_offs[idx]: acc_offs[idx] + plan.acc_numel()]
-                    if ws is not None:                        # the weight gradient runs beside the dgrad chain
-                        ev = torch.cuda.Event()
-                        ev.record(cur_stream)
-                        ws.wait_event(ev)
-                        dz.record_stream(ws)
-                    with torch.cuda.stream(ws if ws is not None else cur_stream):
-                        if layer_cfg[j][3]:
-                            sigma = ctx.sig_of[(sc, j)]
-                            dot = dots[sn_pos[(sc, j)]: sn_pos[(sc, j)] + 1]
-                            # gW_bar = gW / sigma - (sum gW * W_bar) / sigma^2 * u v^T   (W = W_bar / sigma)
-                            unpack_jobs.append(plan.wgrad_acc(x_in, dz, acc, gw, sigma=sigma, dot=dot,
-                                                              w_for_dot=pw.detach()))
-                            u, v = ctx.sn_bufs[sn_pos[(sc, j)]]      # read at backward time: quirk Q1
-                            sn_jobs.append(L.SnGradJob(ptr(gw), ptr(dot), ptr(sigma), ptr(u), ptr(v), pw.shape[0],
-                                                       pw[0].numel()))
-                        else:
-                            unpack_jobs.append(plan.wgrad_acc(x_in, dz, acc, gw))
-                if j > 0 or need_b:
-                    g_next = _empty(tuple(x_in.shape), dt, dev)
-                    plan.dgrad(dz, g_next)
-                else:
-                    g_next = None
-            if need_b and g_next is not None:
-                h, w = ctx.pyr_shapes[i][1:3]
-                d32 = _zeros((B, h, w, 8), torch.float32, dev)
-                call("p2p_uncast_add", ptr(g_next), ptr(d32), B * h * w, 8, 16, dc)
-                dx32[i] = d32
-        if ws is not None:
-            cur_stream.wait_stream(ws)
+            st = scale_streams[i]
+            if st is not None:
+                st.wait_event(ev_ready)
+            with torch.cuda.stream(st if st is not None else lane):
+                cur_stream = torch.cuda.current_stream()
+                ws = helper_stream(dev) if any(need_w) else None      # weight gradients beside this scale's dgrad chain
+                g_next = None           # gradient arriving from the layer above (its dgrad output)
+                for j in reversed(range(nl)):
+                    idx = i * nl + j
+                    plan, x_in, o = plans[idx], inputs[idx], outs[idx]
+                    gu = gouts[idx]
+                    if gu is not None:
+                        if gu.dtype != dt or tuple(gu.shape) != tuple(o.shape):
+                            raise L.P2PError("gradient of a discriminator map must have the map's stored layout")
+                        gu = gu.contiguous()
+                        if st is not None:
+                            gu.record_stream(st)
+                    if gu is None and g_next is None:
+                        continue        # nothing has reached this layer yet
+                    k = sc * nl + j
+                    cout = layer_cfg[j][1]
+                    dz = _empty(tuple(o.shape), dt, dev)
+                    gbias = None
+                    if need_bias[k]:
+                        gbias, ret[2 * k + 1] = _grad_slot(refs[2 * k + 1])
+                    call("p2p_act_bwd", ptr(o), ptr(gu), ptr(g_next), ptr(dz), ptr(gbias), B * plan.Ho * plan.Wo, plan.Co,
+                         cout, plan.act, dc)
+                    if need_w[k]:
+                        pw = refs[2 * k]
+                        gw, ret[2 * k] = _grad_slot(pw)
+                        acc = acc_slab[acc_offs[idx]: acc_offs[idx] + plan.acc_numel()]
+                        if ws is not None:                        # the weight gradient runs beside the dgrad chain
+                            ev = torch.cuda.Event()
+                            ev.record(cur_stream)
+                            ws.wait_event(ev)
+                            dz.record_stream(ws)
+                        with torch.cuda.stream(ws if ws is not None else cur_stream):
+                            if layer_cfg[j][3]:
+                                sigma = ctx.sig_of[(sc, j)]
+                                dot = dots[sn_pos[(sc, j)]: sn_pos[(sc, j)] + 1]
+                                # gW_bar = gW / sigma - (sum gW * W_bar) / sigma^2 * u v^T   (W = W_bar / sigma)
+                                unpack_jobs.append(plan.wgrad_acc(x_in, dz, acc, gw, sigma=sigma, dot=dot,
+                                                                  w_for_dot=pw.detach()))
+                                u, v = ctx.sn_bufs[sn_pos[(sc, j)]]      # read at backward time: quirk Q1
+                                sn_jobs.append(L.SnGradJob(ptr(gw), ptr(dot), ptr(sigma), ptr(u), ptr(v), pw.shape[0],
+                                                           pw[0].numel()))
+                            else:
+                                unpack_jobs.append(plan.wgrad_acc(x_in, dz, acc, gw))
+                    if j > 0 or need_b:
+                        g_next = _empty(tuple(x_in.shape), dt, dev)
+                        plan.dgrad(dz, g_next)
+                    else:
+                        g_next = None
+                if need_b and g_next is not None:
+                    h, w = ctx.pyr_shapes[i][1:3]
+                    d32 = _zeros((B, h, w, 8), torch.float32, dev)
+                    call("p2p_uncast_add", ptr(g_next), ptr(d32), B * h * w, 8, 16, dc)
+                    if st is not None:
+                        d32.record_stream(lane)
+                    dx32[i] = d32
+                if ws is not None:
+                    cur_stream.wait_stream(ws)
+        for st in scale_streams:
+            if st is not None:
+                lane.wait_stream(st)
         if unpack_jobs:
             L.call_multi("p2p_unpack_wgrad_multi", unpack_jobs)
         if sn_jobs:
