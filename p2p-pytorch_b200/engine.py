@@ -805,6 +805,7 @@ def compression_forward(x, convs, prelus, bn, training: bool, bits: Optional[int
 # torchvision vgg19().features[0:30]: output channels of the 3x3 pad-1 convolutions (each followed by ReLU), "M" = 2x2
 # max-pool; Vgg19 taps the activation after features[1], [6], [11], [20], [29] (networks.py:42-51)
 VGG_CFG = (64, 64, "M", 128, 128, "M", 256, 256, 256, 256, "M", 512, 512, 512, 512, "M", 512)
+VGG_CFG_CONV = tuple(v for v in VGG_CFG if v != "M")
 VGG_TAP_AFTER_CONV = (0, 2, 4, 8, 12)          # index (0..12) of the convolution whose ReLU output is tapped
 VGG_WEIGHTS = (1.0 / 32, 1.0 / 16, 1.0 / 8, 1.0 / 4, 1.0)      # networks.py:23
 
@@ -824,48 +825,72 @@ class VGGPack:
         L.call_multi("p2p_pack_weights_multi", jobs, dc)
 
 
+def vgg_stack(pack, biases, img, taps_only: bool):
+    """vgg19.features[0:30] on an NCHW fp32 batch.  Returns (layers, taps): per convolution (plan, input, output,
+    pooling input or None) -- empty when taps_only -- and the five tapped activations in stored layout."""
+    N, _, H, W = img.shape
+    dt, dev = _state["dtype"], img.device
+    dc = L.dtype_code(dt)
+    cur = _empty((N, H, W, 16), dt, dev)
+    call("p2p_nchw_to_nhwc", ptr(img), ptr(cur), N, H, W, 16, 3, dc)
+    layers, taps = [], []
+    h, w, cin, ci = H, W, 3, 0
+    pool_src = None
+    for v in VGG_CFG:
+        if v == "M":
+            nxt = _empty((N, h // 2, w // 2, cur.shape[3]), dt, dev)
+            call("p2p_maxpool2_fwd", ptr(cur), ptr(nxt), N, h, w, cur.shape[3], dc)
+            pool_src = cur
+            cur, h, w = nxt, h // 2, w // 2
+            continue
+        plan = ConvPlan(N, h, w, cur.shape[3], cin, v, 3, 1, 1, L.ACT_RELU)
+        plan.wp, plan.wt = pack.plans[ci].wp, pack.plans[ci].wt
+        out = _empty((N, h, w, plan.Co), dt, dev)
+        plan.fwd(cur, biases[ci], out, None)
+        if not taps_only:
+            layers.append((plan, cur, out, pool_src))
+        pool_src = None
+        if ci in VGG_TAP_AFTER_CONV:
+            taps.append(out)
+        cur, cin, ci = out, v, ci + 1
+    return layers, taps
+
+
 class VGGLossFunction(torch.autograd.Function):
     """loss = sum_i w_i * mean|vgg(x)_i - vgg(y)_i| (VGGLoss.forward, networks.py:25-30), y detached.
 
-    apply(x, y, pack, *biases): x, y [B,3,H,W] fp32 NCHW (H, W multiples of 16); `pack` a VGGPack.  The feature stack
-    runs ONCE on the 2B images of cat(x, y); backward walks only the x half (frozen weights: data-gradients only)."""
+    apply(x, y, pack, target_taps, *biases): x [B,3,H,W] fp32 NCHW (H, W multiples of 16); `pack` a VGGPack.  Either
+    `y` (same shape: the feature stack then runs ONCE on the 2B images of cat(x, y)) or `target_taps` (the five tapped
+    activations of the target, computed ahead of time by vgg_stack: the stack then runs on x alone).  Backward walks only
+    the x half (frozen weights: data-gradients only)."""
 
     @staticmethod
-    def forward(ctx, x, y, pack, *biases):
+    def forward(ctx, x, y, pack, target_taps, *biases):
         L.require_cuda(x, "VGGLoss input")
-        L.require_cuda(y, "VGGLoss target")
-        if x.shape != y.shape or x.dim() != 4 or x.shape[1] != 3 or x.shape[2] % 16 or x.shape[3] % 16:
-            raise L.P2PError("VGGLoss needs two [B,3,H,W] batches with H, W multiples of 16")
+        if x.dim() != 4 or x.shape[1] != 3 or x.shape[2] % 16 or x.shape[3] % 16:
+            raise L.P2PError("VGGLoss needs [B,3,H,W] batches with H, W multiples of 16")
         B, _, H, W = x.shape
         dt, dev = _state["dtype"], x.device
         dc = L.dtype_code(dt)
-        xy = torch.cat((x.detach().float(), y.detach().float()), 0).contiguous()
-        cur = _empty((2 * B, H, W, 16), dt, dev)
-        call("p2p_nchw_to_nhwc", ptr(xy), ptr(cur), 2 * B, H, W, 16, 3, dc)
+        if target_taps is None:
+            L.require_cuda(y, "VGGLoss target")
+            if y.shape != x.shape:
+                raise L.P2PError("VGGLoss: input and target must have the same shape")
+            img = torch.cat((x.detach().float(), y.detach().float()), 0).contiguous()
+        else:
+            img = x.detach().float().contiguous()
+        layers, taps = vgg_stack(pack, biases, img, False)
         loss = torch.zeros((), dtype=torch.float32, device=dev)
-        layers = []                      # per convolution: (plan, input, output, pooled-from) for the backward walk
-        taps = []
-        h, w, cin, ci = H, W, 3, 0
-        pool_src = None
-        for v in VGG_CFG:
-            if v == "M":
-                nxt = _empty((2 * B, h // 2, w // 2, cur.shape[3]), dt, dev)
-                call("p2p_maxpool2_fwd", ptr(cur), ptr(nxt), 2 * B, h, w, cur.shape[3], dc)
-                pool_src = cur
-                cur, h, w = nxt, h // 2, w // 2
-                continue
-            plan = ConvPlan(2 * B, h, w, cur.shape[3], cin, v, 3, 1, 1, L.ACT_RELU)
-            plan.wp, plan.wt = pack.plans[ci].wp, pack.plans[ci].wt
-            out = _empty((2 * B, h, w, plan.Co), dt, dev)
-            plan.fwd(cur, biases[ci], out, None)
-            layers.append((plan, cur, out, pool_src))
-            pool_src = None
-            if ci in VGG_TAP_AFTER_CONV:
-                i = VGG_TAP_AFTER_CONV.index(ci)
-                call("p2p_l1_fwd", ptr(out[:B]), ptr(out[B:]), float(VGG_WEIGHTS[i]), ptr(loss), B * h * w, plan.Co, v, dc)
-                taps.append(i)
-            cur, cin, ci = out, v, ci + 1
-        ctx.layers, ctx.geom = layers, (B, H, W)
+        pairs = []
+        for i, t in enumerate(taps):
+            fake, real = (t[:B], t[B:]) if target_taps is None else (t, target_taps[i])
+            if tuple(real.shape) != tuple(fake.shape) or real.dtype != fake.dtype:
+                raise L.P2PError("VGGLoss: target activations do not match the input's")
+            c_real = VGG_CFG_CONV[VGG_TAP_AFTER_CONV[i]]
+            call("p2p_l1_fwd", ptr(fake), ptr(real), float(VGG_WEIGHTS[i]), ptr(loss), B * fake.shape[1] * fake.shape[2],
+                 fake.shape[3], c_real, dc)
+            pairs.append((fake, real))
+        ctx.layers, ctx.pairs, ctx.geom = layers, pairs, (B, H, W)
         ctx.set_materialize_grads(False)
         return loss
 
@@ -874,8 +899,8 @@ class VGGLossFunction(torch.autograd.Function):
         if ctx.needs_input_grad[1]:
             raise L.P2PError("VGGLoss: the target is detached in the reference (networks.py:29)")
         if g is None or not ctx.needs_input_grad[0]:
-            return (None,) * (3 + 13)
-        layers = ctx.layers
+            return (None,) * (4 + 13)
+        layers, pairs = ctx.layers, ctx.pairs
         B, H, W = ctx.geom
         dt, dev = layers[0][2].dtype, layers[0][2].device
         dc = L.dtype_code(dt)
@@ -889,8 +914,9 @@ class VGGLossFunction(torch.autograd.Function):
             gu = None
             if ci in VGG_TAP_AFTER_CONV:
                 i = VGG_TAP_AFTER_CONV.index(ci)
+                fake, real = pairs[i]
                 gu = _empty(tuple(o_x.shape), dt, dev)
-                call("p2p_l1_bwd", ptr(o_x), ptr(out[B:]), float(VGG_WEIGHTS[i]), ptr(g), ptr(gu), B * d.Ho * d.Wo, plan.Co,
+                call("p2p_l1_bwd", ptr(fake), ptr(real), float(VGG_WEIGHTS[i]), ptr(g), ptr(gu), B * d.Ho * d.Wo, plan.Co,
                      plan.cout_real, dc)
             if gu is None and g_next is None:
                 continue
@@ -907,8 +933,8 @@ class VGGLossFunction(torch.autograd.Function):
             g_next = din
         gx = _empty((B, 3, H, W), torch.float32, dev)
         call("p2p_nhwc_to_nchw", ptr(g_next), ptr(gx), B, H, W, 16, 3, dc)
-        ctx.layers = None
-        return (gx, None, None) + (None,) * 13
+        ctx.layers = ctx.pairs = None
+        return (gx, None, None, None) + (None,) * 13
 
 
 def _half_plan(plan: ConvPlan, B: int) -> ConvPlan:

@@ -425,11 +425,25 @@ class VGGLoss(nn.Module):
         if device is not None:
             self.to(device)
 
-    def forward(self, x, y):
+    def _packed(self):
         ws, bs = self.vgg.conv_params()
         L.require_cuda(ws[0], "VGG19 weights")
         dt = E._state["dtype"]
         key = (dt, E._state["impl"], tuple(w._version for w in ws), tuple(w.data_ptr() for w in ws))
         if self._pack is None or self._pack.key != key:
             self._pack = E.VGGPack(ws, dt)            # frozen banks: packed once, reused by every call
-        return E.VGGLossFunction.apply(x, y, self._pack, *[b.detach() for b in bs])
+        return self._pack, [b.detach() for b in bs]
+
+    @torch.no_grad()
+    def target_features(self, y):
+        """The five tapped activations of the (detached) target, for `forward(x, target_taps=...)`: they do not depend
+        on the generator, so a training loop may compute them before -- or beside -- the generator's forward pass."""
+        L.require_cuda(y, "VGGLoss target")
+        pack, bs = self._packed()
+        return E.vgg_stack(pack, bs, y.detach().float().contiguous(), True)[1]
+
+    def forward(self, x, y=None, target_taps=None):
+        if (y is None) == (target_taps is None):
+            raise ValueError("VGGLoss needs the target image or its precomputed activations (exactly one of them)")
+        pack, bs = self._packed()
+        return E.VGGLossFunction.apply(x, y, pack, target_taps, *bs)

@@ -93,7 +93,7 @@ class Pix2PixTrainer:
         # a second stream gains nothing there).  P2P_LANES=1 / 2 overrides.
         env_lanes = os.environ.get("P2P_LANES")
         self.two_lanes = (self.cuda_graph if two_lanes is None else bool(two_lanes)) if env_lanes is None else env_lanes == "2"
-        self._side = self._side_vgg = None
+        self._side = self._side_vgg = self._side_vgg_lo = None
         if self.cuda_graph:
             self.optimizer_g.make_capturable()
             self.optimizer_d.make_capturable()
@@ -304,6 +304,17 @@ class Pix2PixTrainer:
         last = lambda maps: [s[-1] for s in maps]                                         # noqa: E731
         ones = [1] * 3
         sig1, sig2, sig3 = (net_d.power_iteration() for _ in range(3))                    # passes 1, 2, 3 (:309, :316, :337)
+        vgg_taps = None
+        if self.vgg is not None:
+            # the target's VGG activations do not depend on the generator: low priority, beside G's forward pass
+            if self._side_vgg is None:
+                self._side_vgg = torch.cuda.Stream(device=real_a.device, priority=-1)
+                self._side_vgg_lo = torch.cuda.Stream(device=real_a.device)
+            self._side_vgg_lo.wait_stream(main)
+            with torch.cuda.stream(self._side_vgg_lo):
+                vgg_taps = self.vgg.target_features(real_b)
+                ev_taps = torch.cuda.Event()
+                ev_taps.record(self._side_vgg_lo)
         self.optimizer_g.zero_grad()                                                      # :384
         side.wait_stream(main)
         with torch.cuda.stream(side):                                                     # ---- D lane ----
@@ -323,12 +334,13 @@ class Pix2PixTrainer:
             loss_d = (loss_d_fake + loss_d_real) * 0.5                                    # :320
         loss_vgg = None
         if self.vgg is not None:                           # ---- perceptual lane: beside pass 3 (its backward too) ----
-            if self._side_vgg is None:
-                self._side_vgg = torch.cuda.Stream(device=real_a.device)
             with torch.cuda.stream(self._side_vgg):
                 self._side_vgg.wait_event(ev_fake)
+                self._side_vgg.wait_event(ev_taps)
                 fake_b.record_stream(self._side_vgg)
-                loss_vgg = self.vgg(fake_b, real_b) * 10.0                                # :377
+                for t in vgg_taps:
+                    t.record_stream(self._side_vgg)
+                loss_vgg = self.vgg(fake_b, target_taps=vgg_taps) * 10.0                  # :377
         # ---- G lane ----
         pred_fake = net_d.forward_stored(real_a, fake_b, frozen=True, sigma=sig3)         # :336-337
         ev_pass3 = torch.cuda.Event()

@@ -506,6 +506,14 @@ def test_vgg_loss_matches_reference_golden(case, precision):
         assert rms_relerr(x.grad, torch.from_numpy(gold["grad_x"])) <= 0.35
         assert cosine(x.grad, torch.from_numpy(gold["grad_x"])) >= 0.93
     assert x.grad.shape == x.shape and x.grad.dtype == torch.float32
+    # the target's activations computed ahead of time (what the trainer does beside the generator's forward pass)
+    x2 = torch.tanh(a * 1.5).to(DEV).requires_grad_(True)
+    loss2 = crit(x2, target_taps=crit.target_features(b.to(DEV)))
+    loss2.backward()
+    assert abs(loss2.item() - loss.item()) <= 1e-3 * abs(loss.item())
+    assert rms_relerr(x2.grad, x.grad) <= (1e-4 if precision == "fp32" else 5e-2)
+    with pytest.raises(ValueError):
+        crit(x2)
 
 
 @pytest.mark.parametrize("graph", [False, True], ids=["eager", "graph"])
