@@ -43,7 +43,7 @@ def load_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    """nvidia-smi clocks / throttle reasons sampled every 20 ms; only samples taken while the timed region ran count."""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -53,7 +53,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -62,9 +62,17 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.rows.append([time.time()] + [x.strip() for x in line.split(",")])
 
-    def stop(self):
+    def wait_first_sample(self, keep_busy, limit_s=3.0):
+        """nvidia-smi needs a few hundred ms to start: run `keep_busy()` (untimed extra warm-up steps of the same
+        workload) until its first line has arrived, so that the short timed region is actually covered"""
+        t0 = time.time()
+        while self.proc is not None and not self.rows and time.time() - t0 < limit_s:
+            keep_busy()
+            torch.cuda.synchronize()
+
+    def stop(self, t_begin=None, t_end=None):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -74,7 +82,10 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], None, set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        rows = [r[1:] for r in self.rows if t_begin is None or t_begin <= r[0] <= t_end + 0.03]
+        if not rows:
+            rows = [r[1:] for r in self.rows]
+        for r in rows:
             try:
                 sm.append(float(r[0])); mx = float(r[1])
                 for nm, v in zip(names, r[2:6]):
@@ -359,19 +370,22 @@ def run_ours(args, rank, world, local_rank):
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
+        sampler.wait_first_sample(lambda: step_dev(0)) if world == 1 else time.sleep(0.4)
     barrier()
     l0 = P._lib.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_begin = time.time()
     e0.record()
     for i in range(args.steps):
         out = step_dev(i)
     e1.record()
     barrier()
+    t_end = time.time()
     ms = max_over_ranks(e0.elapsed_time(e1))
     launches = P._lib.launch_count() - l0
     if not args.no_graph:                                    # replayed launches do not pass through the C ABI's counter
         launches = graph_launches * args.steps
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop(t_begin, t_end) if rank == 0 else None
     value = world * B * args.steps / (ms * 1e-3)
 
     # ---- end to end: pinned host bytes -> H2D -> step -> D2H of the result, every step -----------------
