@@ -280,9 +280,6 @@ class Pix2PixTrainer:
         previous u, v, so they run first, in the reference's order, and each pass gets its sigma; everything else is
         the eager order with independent work moved to the second stream (the first-layer sharing between passes 1
         and 3 is dropped: they now run at the same time)."""
-        net_g, net_d, cr = self.net_g, self.net_d, self._c_reals
-        last = lambda maps: [s[-1] for s in maps]                                         # noqa: E731
-        ones = [1] * 3
         outer = torch.cuda.current_stream()
         if self._side is None:
             self._side = torch.cuda.Stream(device=real_a.device)
