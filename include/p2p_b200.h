@@ -168,6 +168,13 @@ int p2p_bn_finalize(const double* stats, int64_t count, const float* gamma, cons
 int p2p_bn_act_store(const void* r, const float* sb, const void* skip, int skip_pad, const float* prelu_a, void* dst,
                      float* out_nchw, int B, int H, int W, int C, int c_real, int act, int up, int pad, int dtype,
                      void* stream);
+/* p2p_bn_finalize followed by p2p_bn_act_store (NHWC destination) as ONE launch: same arguments, same results bit for
+ * bit; `sb` (4*C floats) is still written for the backward kernels.  The bookkeeping kernel is tiny but sits on the
+ * generator's forward chain once per BatchNorm (networks.py:461-490, :433-436). */
+int p2p_bn_finalize_act_store(const double* stats, int64_t count, const float* gamma, const float* beta,
+                              float* running_mean, float* running_var, int64_t* num_batches_tracked, float* sb,
+                              int training, const void* r, const void* skip, int skip_pad, const float* prelu_a, void* dst,
+                              int B, int H, int W, int C, int c_real, int act, int up, int pad, int dtype, void* stream);
 /* Backward of p2p_bn_act_store + BatchNorm, pass 1.  g = fold(dpad) + g1 + g2 (each optional):
  * dpad is the gradient w.r.t. dst (same padded/upsampled geometry), g1/g2 are compact [B,H,W,C] maps,
  * g_nchw an NCHW fp32 gradient (generator output).  dz = g * act'(z), z = scale*r + shift [+ skip];

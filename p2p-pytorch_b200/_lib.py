@@ -75,6 +75,8 @@ SIGNATURES = {
     "p2p_channel_stats": [_vp, _vp, _i64, _i, _i, _vp],
     "p2p_bn_finalize": [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],
     "p2p_bn_act_store": [_vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp],
+    "p2p_bn_finalize_act_store": [_vp, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _i, _vp, _vp,
+                                  _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp],
     "p2p_bn_act_bwd_reduce": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _vp, _vp,
                               _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp],
     "p2p_bn_bwd_apply": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _i, _vp],

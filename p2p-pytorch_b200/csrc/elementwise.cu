@@ -72,12 +72,11 @@ __global__ void __launch_bounds__(256) channel_stats_kernel(const T* __restrict_
 // =================================================================================================
 // BatchNorm bookkeeping
 // =================================================================================================
-__global__ void bn_finalize_kernel(const double* __restrict__ stats, int64_t count, const float* __restrict__ gamma,
-                                   const float* __restrict__ beta, float* running_mean, float* running_var,
-                                   int64_t* nbt, float* __restrict__ sb, int c_real, int C, int training) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c == 0 && training && nbt != nullptr) *nbt += 1;
-  if (c >= C) return;
+// one channel of the BatchNorm bookkeeping: batch statistics (training) or running statistics (eval) -> scale / shift /
+// mean / 1/std; `update` (one thread per channel, once per layer) also moves the running buffers
+__device__ __forceinline__ void bn_channel(const double* __restrict__ stats, int64_t count, const float* __restrict__ gamma,
+                                           const float* __restrict__ beta, float* running_mean, float* running_var, int c,
+                                           int c_real, int C, int training, bool update, float out[4]) {
   float scale = 0.f, shift = 0.f, mean = 0.f, invstd = 0.f;
   if (c < c_real) {
     if (training) {
@@ -86,7 +85,7 @@ __global__ void bn_finalize_kernel(const double* __restrict__ stats, int64_t cou
       var = var < 0.0 ? 0.0 : var;
       mean = (float)m;
       invstd = (float)(1.0 / sqrt(var + 1e-5));
-      if (running_mean != nullptr) {
+      if (update && running_mean != nullptr) {
         const double unb = count > 1 ? var * (double)count / (double)(count - 1) : var;
         running_mean[c] = 0.9f * running_mean[c] + 0.1f * mean;
         running_var[c] = 0.9f * running_var[c] + 0.1f * (float)unb;
@@ -98,10 +97,21 @@ __global__ void bn_finalize_kernel(const double* __restrict__ stats, int64_t cou
     scale = gamma[c] * invstd;
     shift = beta[c] - mean * scale;
   }
-  sb[c] = scale;
-  sb[C + c] = shift;
-  sb[2 * C + c] = mean;
-  sb[3 * C + c] = invstd;
+  out[0] = scale; out[1] = shift; out[2] = mean; out[3] = invstd;
+}
+
+__global__ void bn_finalize_kernel(const double* __restrict__ stats, int64_t count, const float* __restrict__ gamma,
+                                   const float* __restrict__ beta, float* running_mean, float* running_var,
+                                   int64_t* nbt, float* __restrict__ sb, int c_real, int C, int training) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c == 0 && training && nbt != nullptr) *nbt += 1;
+  if (c >= C) return;
+  float o[4];
+  bn_channel(stats, count, gamma, beta, running_mean, running_var, c, c_real, C, training, true, o);
+  sb[c] = o[0];
+  sb[C + c] = o[1];
+  sb[2 * C + c] = o[2];
+  sb[3 * C + c] = o[3];
 }
 
 __device__ __forceinline__ float act_fwd(float z, int act, float a) {
@@ -150,6 +160,61 @@ __global__ void bn_act_store_kernel(const T* __restrict__ r, const float* __rest
     for (int k = 0; k < 8; ++k) {
       const int c = c8 * 8 + k;
       float z = sb != nullptr ? fmaf(v[k], sb[c], sb[C + c]) : v[k];
+      if (skip != nullptr) z += sk[k];
+      v[k] = act_fwd(z, act, a);
+    }
+    st8(dst + (size_t)i * 8, v);
+  }
+}
+
+// bn_finalize + bn_act_store in one launch (the tiny bookkeeping kernel sits on the generator's critical path 24 times
+// per forward): every block derives scale / shift of all C <= 512 channels from the statistics into shared memory --
+// the same arithmetic as bn_finalize_kernel, so the results are bit-identical -- and block 0 also writes `sb` for the
+// backward pass and moves the running buffers.
+template <typename T, int ACT>
+__global__ void __launch_bounds__(256)
+    bn_finalize_act_store_kernel(const double* __restrict__ stats, int64_t count, const float* __restrict__ gamma,
+                                 const float* __restrict__ beta, float* running_mean, float* running_var, int64_t* nbt,
+                                 float* __restrict__ sb, int c_real, int training, const T* __restrict__ r,
+                                 const T* __restrict__ skip, int skip_pad, const float* __restrict__ prelu_a,
+                                 T* __restrict__ dst, int B, int H, int W, int C, int up, int pad) {
+  __shared__ float s_scale[512], s_shift[512];
+  const bool first = blockIdx.x == 0;
+  if (first && threadIdx.x == 0 && training && nbt != nullptr) *nbt += 1;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float o[4];
+    bn_channel(stats, count, gamma, beta, running_mean, running_var, c, c_real, C, training, first, o);
+    s_scale[c] = o[0];
+    s_shift[c] = o[1];
+    if (first) {
+      sb[c] = o[0];
+      sb[C + c] = o[1];
+      sb[2 * C + c] = o[2];
+      sb[3 * C + c] = o[3];
+    }
+  }
+  __syncthreads();
+  constexpr int act = ACT;
+  const int C8 = C >> 3, Hu = H * up, Wu = W * up, Hd = Hu + 2 * pad, Wd = Wu + 2 * pad;
+  const int sh = up == 2 ? 1 : 0;
+  const float a = prelu_a != nullptr ? *prelu_a : 0.f;
+  const uint32_t total = (uint32_t)B * Hd * Wd * C8;   // < 2^31, checked by the caller
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % (uint32_t)C8);
+    uint32_t p = i / (uint32_t)C8;
+    const int dx = (int)(p % (uint32_t)Wd); p /= (uint32_t)Wd;
+    const int dy = (int)(p % (uint32_t)Hd);
+    const int n = (int)(p / (uint32_t)Hd);
+    const int sy = reflect_idx(dy - pad, Hu) >> sh, sx = reflect_idx(dx - pad, Wu) >> sh;
+    float v[8];
+    ld8(r + (((int64_t)n * H + sy) * W + sx) * C + c8 * 8, v);
+    float sk[8];
+    if (skip != nullptr)
+      ld8(skip + (((int64_t)n * (H + 2 * skip_pad) + sy + skip_pad) * (W + 2 * skip_pad) + sx + skip_pad) * C + c8 * 8, sk);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int c = c8 * 8 + k;
+      float z = fmaf(v[k], s_scale[c], s_shift[c]);
       if (skip != nullptr) z += sk[k];
       v[k] = act_fwd(z, act, a);
     }
@@ -1022,6 +1087,33 @@ int p2p_bn_act_store(const void* r, const float* sb, const void* skip, int skip_
     default: P2P_REQUIRE(false, "unknown activation");
   }
 #undef P2P_STORE
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_bn_finalize_act_store(const double* stats, int64_t count, const float* gamma, const float* beta,
+                              float* running_mean, float* running_var, int64_t* num_batches_tracked, float* sb,
+                              int training, const void* r, const void* skip, int skip_pad, const float* prelu_a, void* dst,
+                              int B, int H, int W, int C, int c_real, int act, int up, int pad, int dtype, void* stream) {
+  P2P_REQUIRE(gamma && beta && sb && r && dst, "null pointer");
+  P2P_REQUIRE(training ? (stats != nullptr && count > 0) : (running_mean && running_var), "missing statistics");
+  P2P_REQUIRE(C % 16 == 0 && C <= 512 && (up == 1 || up == 2) && pad >= 0, "bad geometry");
+  P2P_REQUIRE(pad < H * up && pad < W * up, "reflection pad must be smaller than the image");
+  P2P_REQUIRE(act != P2P_ACT_PRELU || prelu_a, "PReLU needs its slope");
+  const int64_t total = (int64_t)B * (H * up + 2 * pad) * (W * up + 2 * pad) * (C / 8);
+  P2P_REQUIRE(total < (1LL << 31), "tensor too large");
+#define P2P_FSTORE(ACT_)                                                                                     \
+  P2P_DISPATCH(dtype, bn_finalize_act_store_kernel<T, ACT_><<<ew_grid(total), 256, 0, as_stream(stream)>>>( \
+                          stats, count, gamma, beta, running_mean, running_var, num_batches_tracked, sb, c_real,   \
+                          training, (const T*)r, (const T*)skip, skip_pad, prelu_a, (T*)dst, B, H, W, C, up, pad););
+  switch (act) {
+    case P2P_ACT_NONE: P2P_FSTORE(P2P_ACT_NONE) break;
+    case P2P_ACT_RELU: P2P_FSTORE(P2P_ACT_RELU) break;
+    case P2P_ACT_PRELU: P2P_FSTORE(P2P_ACT_PRELU) break;
+    case P2P_ACT_LRELU: P2P_FSTORE(P2P_ACT_LRELU) break;
+    case P2P_ACT_TANH: P2P_FSTORE(P2P_ACT_TANH) break;
+    default: P2P_REQUIRE(false, "unknown activation");
+  }
+#undef P2P_FSTORE
   P2P_LAUNCH_CHECK();
 }
 

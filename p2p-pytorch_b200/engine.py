@@ -13,6 +13,7 @@ fresh gradient tensor is returned the usual way.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import List, Optional, Sequence
 
 import torch
@@ -311,8 +312,21 @@ class GeneratorFunction(torch.autograd.Function):
             else:
                 plan.fwd(cur, b, r, stats)
             sb = _empty((4 * Co,), torch.float32, dev)
-            call("p2p_bn_finalize", ptr(stats), B * Ho * Wo, ptr(gamma), ptr(beta), ptr(rm), ptr(rv), ptr(nbt), ptr(sb),
-                 cout, Co, 1 if training else 0)
+            # the BatchNorm bookkeeping rides in the launch that applies it (p2p_bn_finalize_act_store) wherever the
+            # stage's output is a stored map; only the last stage (NCHW output) keeps the separate kernel
+            fused_store = li != G_N - 1 and os.environ.get("P2P_FUSED_BN_STORE", "1") != "0"
+            if not fused_store:
+                call("p2p_bn_finalize", ptr(stats), B * Ho * Wo, ptr(gamma), ptr(beta), ptr(rm), ptr(rv), ptr(nbt), ptr(sb),
+                     cout, Co, 1 if training else 0)
+
+            def bn_store(skip, skip_pad, dst, up, pad):
+                if fused_store:
+                    call("p2p_bn_finalize_act_store", ptr(stats), B * Ho * Wo, ptr(gamma), ptr(beta), ptr(rm), ptr(rv),
+                         ptr(nbt), ptr(sb), 1 if training else 0, ptr(r), ptr(skip), skip_pad, ptr(prelu), ptr(dst), B, Ho,
+                         Wo, Co, cout, act, up, pad, dc)
+                else:
+                    call("p2p_bn_act_store", ptr(r), ptr(sb), ptr(skip), skip_pad, ptr(prelu), ptr(dst), None, B, Ho, Wo,
+                         Co, cout, act, up, pad, dc)
             st = _Stage()
             st.li, st.plan, st.x_in, st.r, st.sb, st.act, st.role = li, plan, cur, r, sb, act, role
             st.fat = fat if li == G_N - 1 else None
@@ -332,8 +346,7 @@ class GeneratorFunction(torch.autograd.Function):
                 # res9's output stays compact: its only consumer is the long-skip add, not a convolution
                 st.up, st.pad = 1, 0
                 y9 = _empty((B, Ho, Wo, Co), dt, dev)
-                call("p2p_bn_act_store", ptr(r), ptr(sb), ptr(st.skip), st.skip_pad, ptr(prelu), ptr(y9), None, B, Ho,
-                     Wo, Co, cout, act, 1, 0, dc)
+                bn_store(st.skip, st.skip_pad, y9, 1, 0)
                 stages.append(st)
                 # y = LeakyReLU(res + residual) (networks.py:514-515), then nearest x2 + reflect 1 for deconv3
                 ls = _Stage()
@@ -349,8 +362,7 @@ class GeneratorFunction(torch.autograd.Function):
                 nxt_name, nxt_k = G_LAYERS[li + 1][0], G_LAYERS[li + 1][3]
                 st.up, st.pad = (2 if nxt_name in ("deconv3", "deconv2") else 1), nxt_k // 2
                 dst = _empty((B, Ho * st.up + 2 * st.pad, Wo * st.up + 2 * st.pad, Co), dt, dev)
-                call("p2p_bn_act_store", ptr(r), ptr(sb), ptr(st.skip), st.skip_pad, ptr(prelu), ptr(dst), None, B, Ho,
-                     Wo, Co, cout, act, st.up, st.pad, dc)
+                bn_store(st.skip, st.skip_pad, dst, st.up, st.pad)
                 stages.append(st)
                 cur, producer = dst, st
                 if name == "conv3":

@@ -416,3 +416,39 @@ def test_decode_u8_is_bit_identical_to_totensor_normalize():
     dst2 = torch.empty(u8.numel(), device=DEV)
     L.call("p2p_decode_u8", src.data_ptr(), dst2.data_ptr(), None, u8.numel(), 3)
     assert torch.equal(dst2, dst)
+
+
+@pytest.mark.parametrize("dt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("training", [True, False])
+def test_fused_bn_finalize_act_store_is_bit_identical(dt, training):
+    """p2p_bn_finalize_act_store == p2p_bn_finalize followed by p2p_bn_act_store: stored map, `sb`, running buffers and
+    the batch counter, bit for bit (skip connection, upsample and reflection pad on)."""
+    torch.manual_seed(11)
+    B, Cc, H, W, up, pad, act = 3, 64, 10, 14, 2, 1, L.ACT_PRELU
+    dc = L.dtype_code(dt)
+    r = (torch.randn(B, H, W, Cc, device=DEV) * 2 + 0.3).to(dt)
+    skip = torch.randn(B, H + 2, W + 2, Cc, device=DEV).to(dt)
+    gamma, beta = torch.rand(Cc, device=DEV) + 0.5, torch.randn(Cc, device=DEV)
+    a = torch.tensor([0.25], device=DEV)
+    stats = torch.zeros(2 * Cc, dtype=torch.float64, device=DEV)
+    L.call("p2p_channel_stats", r.data_ptr(), stats.data_ptr(), B * H * W, Cc, dc)
+    res = []
+    for fused in (False, True):
+        rm, rv = torch.full((Cc,), 0.1, device=DEV), torch.full((Cc,), 1.3, device=DEV)
+        nbt = torch.zeros((), dtype=torch.int64, device=DEV)
+        sb = torch.zeros(4 * Cc, device=DEV)
+        dst = torch.zeros(B, H * up + 2 * pad, W * up + 2 * pad, Cc, dtype=dt, device=DEV)
+        if fused:
+            L.call("p2p_bn_finalize_act_store", stats.data_ptr(), B * H * W, gamma.data_ptr(), beta.data_ptr(), rm.data_ptr(),
+                   rv.data_ptr(), nbt.data_ptr(), sb.data_ptr(), int(training), r.data_ptr(), skip.data_ptr(), 1,
+                   a.data_ptr(), dst.data_ptr(), B, H, W, Cc, Cc, act, up, pad, dc)
+        else:
+            L.call("p2p_bn_finalize", stats.data_ptr(), B * H * W, gamma.data_ptr(), beta.data_ptr(), rm.data_ptr(),
+                   rv.data_ptr(), nbt.data_ptr(), sb.data_ptr(), Cc, Cc, int(training))
+            L.call("p2p_bn_act_store", r.data_ptr(), sb.data_ptr(), skip.data_ptr(), 1, a.data_ptr(), dst.data_ptr(), None,
+                   B, H, W, Cc, Cc, act, up, pad, dc)
+        torch.cuda.synchronize()
+        res.append((dst, sb, rm, rv, nbt))
+    for x, y in zip(*res):
+        assert torch.equal(x, y)
+    assert res[1][4].item() == (1 if training else 0)
