@@ -282,6 +282,19 @@ int p2p_l1_fwd(const void* f, const void* r, float weight, float* loss, int64_t 
 int p2p_l1_bwd(const void* f, const void* r, float weight, const float* gscale, void* g, int64_t pixels, int C,
                int c_real, int dtype, void* stream);
 /* total variation of an NCHW fp32 image batch: *loss += mean|dx| + mean|dy|; g += gscale * d loss / d x. */
+/* The LSGAN / feature-matching sums over several stored maps in ONE launch (the objective touches 15 maps forward and
+ * 15 backward per discriminator pass: networks.py:840-850 over 3 scales, train.py:344-351 over 12 maps).  A job is one
+ * p2p_mse_const_* (mode 0: against `target`) or p2p_l1_* (mode 1: against map `r`) call: `coef` = the map's weight (the
+ * mean over pixels x c_real is applied inside), `g` = where backward writes the map's gradient (forward ignores it),
+ * `blocks` is filled in by the library.  `jobs` is a HOST array, n <= P2P_MULTI_MAX. */
+typedef struct p2p_loss_job {
+  const void* p; const void* r; void* g;
+  float target, coef;
+  int64_t pixels;
+  int32_t C, c_real, mode, blocks;
+} p2p_loss_job;
+int p2p_map_loss_multi_fwd(int n, const p2p_loss_job* jobs, float* loss, int dtype, void* stream);
+int p2p_map_loss_multi_bwd(int n, const p2p_loss_job* jobs, const float* gscale, int dtype, void* stream);
 int p2p_tv_fwd(const float* x, float* loss, int B, int C, int H, int W, void* stream);
 int p2p_tv_bwd_add(const float* x, const float* gscale, float* g, int B, int C, int H, int W, void* stream);
 

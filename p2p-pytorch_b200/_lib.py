@@ -40,6 +40,12 @@ class UnpackJob(C.Structure):
                 ("dot", C.c_void_p)] + [(n, C.c_int32) for n in ("co_real", "ci_real", "Co", "Ci", "kh", "kw")]
 
 
+class LossJob(C.Structure):
+    """struct p2p_loss_job"""
+    _fields_ = [("p", C.c_void_p), ("r", C.c_void_p), ("g", C.c_void_p), ("target", C.c_float), ("coef", C.c_float),
+                ("pixels", C.c_int64), ("C", C.c_int32), ("c_real", C.c_int32), ("mode", C.c_int32), ("blocks", C.c_int32)]
+
+
 class SnGradJob(C.Structure):
     """struct p2p_sn_grad_job"""
     _fields_ = [("grad_wbar", C.c_void_p), ("dot", C.c_void_p), ("sigma", C.c_void_p), ("u", C.c_void_p),
@@ -106,6 +112,8 @@ SIGNATURES = {
     "p2p_mse_flat_bwd": [_vp, _f, _f, _vp, _vp, _i64, _vp],
     "p2p_l1_fwd": [_vp, _vp, _f, _vp, _i64, _i, _i, _i, _vp],
     "p2p_l1_bwd": [_vp, _vp, _f, _vp, _vp, _i64, _i, _i, _i, _vp],
+    "p2p_map_loss_multi_fwd": [_i, _vp, _vp, _i, _vp],
+    "p2p_map_loss_multi_bwd": [_i, _vp, _vp, _i, _vp],
     "p2p_tv_fwd": [_vp, _vp, _i, _i, _i, _i, _vp],
     "p2p_tv_bwd_add": [_vp, _vp, _vp, _i, _i, _i, _i, _vp],
     "p2p_pack_weights_multi": [_i, _vp, _i, _vp],

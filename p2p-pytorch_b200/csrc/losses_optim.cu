@@ -58,6 +58,70 @@ __global__ void __launch_bounds__(256) map_loss_bwd_kernel(const T* __restrict__
   }
 }
 
+// ---- the same two kernels over up to P2P_MULTI_MAX maps in ONE launch (blockIdx.y = map): the objective touches 15
+// maps forward and 15 backward per pass, 3-10 us each, in series on the generator's critical path -------------------
+struct LossTable {
+  p2p_loss_job j[P2P_MULTI_MAX];
+};
+template <typename T>
+__global__ void __launch_bounds__(256) map_loss_multi_fwd_kernel(const __grid_constant__ LossTable tb, float* __restrict__ loss) {
+  const p2p_loss_job& jb = tb.j[blockIdx.y];
+  const int C8 = jb.C >> 3;
+  const int64_t total = jb.pixels * C8;
+  if ((int64_t)blockIdx.x * blockDim.x >= total) return;
+  const T* p = (const T*)jb.p;
+  const T* r = (const T*)jb.r;
+  const int64_t stride = (int64_t)jb.blocks * blockDim.x;
+  if (blockIdx.x >= (unsigned)jb.blocks) return;
+  float acc = 0.f;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int c8 = (int)(i % C8);
+    if (c8 * 8 >= jb.c_real) continue;
+    float a[8], b[8];
+    ld8(p + i * 8, a);
+    if (jb.mode == 1) ld8(r + i * 8, b);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      if (c8 * 8 + k < jb.c_real) {
+        const float d = jb.mode == 0 ? a[k] - jb.target : a[k] - b[k];
+        acc += jb.mode == 0 ? d * d : fabsf(d);
+      }
+    }
+  }
+  const float tot = block_sum<float>(acc);
+  if (threadIdx.x == 0) atomicAdd(loss, tot * jb.coef);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) map_loss_multi_bwd_kernel(const __grid_constant__ LossTable tb,
+                                                                 const float* __restrict__ gscale) {
+  const p2p_loss_job& jb = tb.j[blockIdx.y];
+  if (blockIdx.x >= (unsigned)jb.blocks) return;
+  const int C8 = jb.C >> 3;
+  const int64_t total = jb.pixels * C8;
+  const T* p = (const T*)jb.p;
+  const T* r = (const T*)jb.r;
+  T* g = (T*)jb.g;
+  const float s = jb.coef * (gscale != nullptr ? *gscale : 1.f);
+  const int64_t stride = (int64_t)jb.blocks * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int c8 = (int)(i % C8);
+    float a[8], b[8], o[8];
+    ld8(p + i * 8, a);
+    if (jb.mode == 1) ld8(r + i * 8, b);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      float v = 0.f;
+      if (c8 * 8 + k < jb.c_real) {
+        if (jb.mode == 0) v = 2.f * (a[k] - jb.target) * s;
+        else { const float d = a[k] - b[k]; v = d > 0.f ? s : (d < 0.f ? -s : 0.f); }
+      }
+      o[k] = v;
+    }
+    st8(g + i * 8, o);
+  }
+}
+
 // ---- same on a flat fp32 array (drop-in GANLoss on tensors that did not come from this library) -------
 __global__ void __launch_bounds__(256) mse_flat_fwd_kernel(const float* __restrict__ p, float target, float coef,
                                                            float* __restrict__ loss, int64_t n) {
@@ -262,6 +326,40 @@ int p2p_l1_bwd(const void* f, const void* r, float weight, const float* gscale, 
   const float coef = weight / (float)((double)pixels * c_real);
   P2P_DISPATCH(dtype, map_loss_bwd_kernel<T, 1><<<red_grid(pixels * (C / 8)), 256, 0, as_stream(stream)>>>(
                           (const T*)f, (const T*)r, 0.f, coef, gscale, (T*)g, pixels, C, c_real););
+  P2P_LAUNCH_CHECK();
+}
+
+static int fill_loss_table(int n, const p2p_loss_job* jobs, LossTable* tb, int* max_blocks) {
+  P2P_REQUIRE(n >= 1 && n <= P2P_MULTI_MAX && jobs != nullptr, "1..P2P_MULTI_MAX jobs expected");
+  *max_blocks = 1;
+  for (int i = 0; i < n; ++i) {
+    p2p_loss_job j = jobs[i];
+    P2P_REQUIRE(j.p && j.pixels > 0 && j.C % 8 == 0 && j.c_real <= j.C && (j.mode == 0 || (j.mode == 1 && j.r)),
+                "bad loss job");
+    // coef arrives as the job's weight; the mean over the real elements is folded in here, like the single-map calls
+    j.coef = j.coef / (float)((double)j.pixels * j.c_real);
+    j.blocks = red_grid(j.pixels * (j.C / 8));
+    if (j.blocks > *max_blocks) *max_blocks = j.blocks;
+    tb->j[i] = j;
+  }
+  return 0;
+}
+
+int p2p_map_loss_multi_fwd(int n, const p2p_loss_job* jobs, float* loss, int dtype, void* stream) {
+  LossTable tb{};
+  int mb = 1;
+  if (int e = fill_loss_table(n, jobs, &tb, &mb)) return e;
+  P2P_REQUIRE(loss != nullptr, "null pointer");
+  P2P_DISPATCH(dtype, map_loss_multi_fwd_kernel<T><<<dim3(mb, n), 256, 0, as_stream(stream)>>>(tb, loss););
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_map_loss_multi_bwd(int n, const p2p_loss_job* jobs, const float* gscale, int dtype, void* stream) {
+  LossTable tb{};
+  int mb = 1;
+  if (int e = fill_loss_table(n, jobs, &tb, &mb)) return e;
+  for (int i = 0; i < n; ++i) P2P_REQUIRE(jobs[i].g != nullptr, "null gradient pointer");
+  P2P_DISPATCH(dtype, map_loss_multi_bwd_kernel<T><<<dim3(mb, n), 256, 0, as_stream(stream)>>>(tb, gscale););
   P2P_LAUNCH_CHECK();
 }
 

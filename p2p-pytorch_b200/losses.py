@@ -22,16 +22,23 @@ class _MapLoss(torch.autograd.Function):
     """sum_i weight_i * mean(f(p_i [, r_i])) over stored maps; kind 'mse' (vs constant) or 'l1' (vs r_i)."""
 
     @staticmethod
+    def _jobs(kind, target, weights, c_reals, preds, refs, grads):
+        jobs = []
+        for i, p in enumerate(preds):
+            B, H, W, C = p.shape
+            jobs.append(L.LossJob(ptr(p), ptr(refs[i]) if kind == "l1" else None, ptr(grads[i]) if grads else None,
+                                  float(target), float(weights[i]), B * H * W, C, c_reals[i], 1 if kind == "l1" else 0, 0))
+        return jobs
+
+    @staticmethod
     def forward(ctx, kind, target, weights, c_reals, n, *maps):
         preds, refs = maps[:n], maps[n:]
         loss = _scalar(preds[0].device)
-        for i, p in enumerate(preds):
-            B, H, W, C = p.shape
-            dc = L.dtype_code(p.dtype)
-            if kind == "mse":
-                call("p2p_mse_const_fwd", ptr(p), float(target), float(weights[i]), ptr(loss), B * H * W, C, c_reals[i], dc)
-            else:
-                call("p2p_l1_fwd", ptr(p), ptr(refs[i]), float(weights[i]), ptr(loss), B * H * W, C, c_reals[i], dc)
+        if any(p.dtype != preds[0].dtype for p in preds):
+            raise L.P2PError("all maps of one loss must have the same dtype")
+        # one launch for all maps (p2p_map_loss_multi_fwd), <= P2P_MULTI_MAX maps per launch
+        L.call_multi("p2p_map_loss_multi_fwd", _MapLoss._jobs(kind, target, weights, c_reals, preds, refs, None), ptr(loss),
+                     L.dtype_code(preds[0].dtype))
         ctx.kind, ctx.target, ctx.weights, ctx.c_reals, ctx.n = kind, target, weights, c_reals, n
         ctx.maps = maps
         return loss
@@ -41,21 +48,15 @@ class _MapLoss(torch.autograd.Function):
         n, maps = ctx.n, ctx.maps
         preds, refs = maps[:n], maps[n:]
         g = g.contiguous().float()
-        outs = []
-        for i, p in enumerate(preds):
-            if not ctx.needs_input_grad[5 + i]:
-                outs.append(None)
-                continue
-            B, H, W, C = p.shape
-            dc = L.dtype_code(p.dtype)
-            gp = torch.empty_like(p)
-            if ctx.kind == "mse":
-                call("p2p_mse_const_bwd", ptr(p), float(ctx.target), float(ctx.weights[i]), ptr(g), ptr(gp), B * H * W,
-                     C, ctx.c_reals[i], dc)
-            else:
-                call("p2p_l1_bwd", ptr(p), ptr(refs[i]), float(ctx.weights[i]), ptr(g), ptr(gp), B * H * W, C,
-                     ctx.c_reals[i], dc)
-            outs.append(gp)
+        need = [i for i in range(n) if ctx.needs_input_grad[5 + i]]
+        outs = [None] * n
+        if need:
+            for i in need:
+                outs[i] = torch.empty_like(preds[i])
+            jobs = _MapLoss._jobs(ctx.kind, ctx.target, [ctx.weights[i] for i in need], [ctx.c_reals[i] for i in need],
+                                  [preds[i] for i in need], [refs[i] for i in need] if ctx.kind == "l1" else [],
+                                  [outs[i] for i in need])
+            L.call_multi("p2p_map_loss_multi_bwd", jobs, ptr(g), L.dtype_code(preds[0].dtype))
         return (None, None, None, None, None, *outs, *([None] * len(refs)))
 
 
