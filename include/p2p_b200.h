@@ -239,6 +239,9 @@ int p2p_kx_scatter(const void* dy, void* a, int N, int H, int Wo, int Wa, int kw
  * generate_dataset.py:29-34 does for train.py:297, to `compressed` (may be NULL); both NCHW fp32 [B,3,H,W]. */
 int p2p_c_output(const void* res, const float* x, float* y, float* compressed, int B, int H, int W, int bits, int dtype,
                  void* stream);
+/* Zero `bytes` bytes at `p` (16-byte aligned) with 16-byte stores: the split-K weight-gradient accumulators handed to
+ * p2p_conv_wgrad must start at zero (what autograd's freshly allocated .grad does for the reference's conv backward). */
+int p2p_zero_fill(void* p, int64_t bytes, void* stream);
 /* 8-bit images -> the fp32 tensors of the iteration: dst = (src / 255 - 0.5) / 0.5, i.e. ToTensor + Normalize(0.5, 0.5)
  * of dataset.py:19-20,30-40 with torchvision's fp32 operation order (bit-identical), and, when `quant` is not NULL,
  * quant = compress(dst * 0.5 + 0.5, bits) of generate_dataset.py:29-34 (the quantiser in front of the generator,

@@ -101,6 +101,7 @@ SIGNATURES = {
     "p2p_c_output": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp],
     "p2p_maxpool2_fwd": [_vp, _vp, _i, _i, _i, _i, _i, _vp],
     "p2p_maxpool2_bwd": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp],
+    "p2p_zero_fill": [_vp, _i64, _vp],
     "p2p_decode_u8": [_vp, _vp, _vp, _i64, _i, _vp],
     "p2p_nhwc_to_nchw": [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp],
     "p2p_nchw_to_nhwc": [_vp, _vp, _i, _i, _i, _i, _i, _i, _vp],

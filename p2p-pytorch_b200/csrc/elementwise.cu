@@ -919,6 +919,18 @@ __global__ void __launch_bounds__(256) c_output_kernel(const T* __restrict__ res
 }
 
 // ---------------------------------------------------------------------------------------------------
+// Zero-fill with 16-byte stores.  The weight-gradient accumulators (split-K atomics) must start at zero: 33 MB per
+// discriminator backward pass, 11.5 MB for the generator; torch.zeros() on a tensor of that size launches a
+// byte-granular fill kernel that ncu times at ~70 us (0.47 TB/s).
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) zero_fill_kernel(uint4* __restrict__ p, int64_t n16, uint8_t* __restrict__ tail,
+                                                        int n_tail) {
+  const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (int64_t)gridDim.x * blockDim.x) p[i] = z;
+  if (blockIdx.x == 0 && (int)threadIdx.x < n_tail) tail[threadIdx.x] = 0;
+}
+
+// ---------------------------------------------------------------------------------------------------
 // 8-bit image batch -> the fp32 tensors the iteration consumes (dataset.py:19-20,30-40: ToTensor = x / 255,
 // Normalize(0.5, 0.5) = (t - 0.5) / 0.5), same fp32 operations in the same order as torchvision, and optionally
 // the 3-bit quantised generator input compress(b * 0.5 + 0.5, bits) (generate_dataset.py:29-34) in the same pass.
@@ -1282,6 +1294,16 @@ int p2p_nchw_to_nhwc(const float* in, void* out, int B, int H, int W, int C, int
   P2P_REQUIRE(in && out && c_real <= C && C % 8 == 0, "null pointer");
   P2P_DISPATCH(dtype, nchw_to_nhwc_kernel<T><<<ew_grid((int64_t)B * H * W * (C / 8)), 256, 0, as_stream(stream)>>>(
                           in, (T*)out, B, H, W, C, c_real););
+  P2P_LAUNCH_CHECK();
+}
+
+int p2p_zero_fill(void* p, int64_t bytes, void* stream) {
+  P2P_REQUIRE(p != nullptr && bytes > 0 && ((uintptr_t)p % 16 == 0), "16-byte aligned buffer expected");
+  const int64_t n16 = bytes / 16;
+  int64_t blocks = (n16 + 255) / 256;
+  if (blocks < 1) blocks = 1;
+  if (blocks > kSMs * 8) blocks = kSMs * 8;
+  zero_fill_kernel<<<(int)blocks, 256, 0, as_stream(stream)>>>((uint4*)p, n16, (uint8_t*)p + n16 * 16, (int)(bytes - n16 * 16));
   P2P_LAUNCH_CHECK();
 }
 

@@ -80,7 +80,12 @@ def _empty(shape, dtype, dev):
 
 
 def _zeros(shape, dtype, dev):
-    return torch.zeros(shape, dtype=dtype, device=dev)
+    t = torch.empty(shape, dtype=dtype, device=dev)
+    nbytes = t.numel() * t.element_size()
+    if nbytes >= (1 << 20) and t.data_ptr() % 16 == 0:
+        call("p2p_zero_fill", ptr(t), nbytes)          # large slabs: 16-byte stores (torch's fill runs at 0.5 TB/s here)
+        return t
+    return t.zero_()
 
 
 def _grad_slot(p: torch.Tensor):

@@ -452,3 +452,12 @@ def test_fused_bn_finalize_act_store_is_bit_identical(dt, training):
     for x, y in zip(*res):
         assert torch.equal(x, y)
     assert res[1][4].item() == (1 if training else 0)
+
+
+def test_zero_fill():
+    for n in (1 << 20, (1 << 22) + 7, 33_214_016):
+        t = torch.full((n + 32,), 7, dtype=torch.uint8, device=DEV)
+        L.call("p2p_zero_fill", t.data_ptr() + 16, n)
+        torch.cuda.synchronize()
+        assert t[16:16 + n].count_nonzero().item() == 0
+        assert t[:16].eq(7).all().item() and t[16 + n:].eq(7).all().item()
