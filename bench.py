@@ -464,7 +464,7 @@ def run_ours(args, rank, world, local_rank):
 
     if rank != 0:
         return
-    hbm, tf_burst, tf_sust, which = load_peaks()
+    _hbm, tf_burst, tf_sust, which = load_peaks()
     flop_img = (G_FWD_FLOP_PER_IMG_256 if infer else FLOP_PER_IMG_256 + (VGG_FLOP_PER_IMG_256 if args.with_vgg else 0.0)) \
         * (S / 256.0) ** 2
     line = {"metric": metric_name(args), "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,

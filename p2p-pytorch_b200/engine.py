@@ -302,7 +302,7 @@ class GeneratorFunction(torch.autograd.Function):
         stats_slab = _zeros((sum(2 * pk.Co for pk in packs),), torch.float64, dev) if training else None
         stats_off = 0
         for li, (name, _bn, cout, k, stride, act, role) in enumerate(G_LAYERS):
-            w, b, gamma, beta = params[4 * li: 4 * li + 4]
+            _w, b, gamma, beta = params[4 * li: 4 * li + 4]
             rm, rv, nbt = buffers[li]
             plan = ConvPlan(B, cur.shape[1], cur.shape[2], cur.shape[3], cin_real, cout, k, stride, 0)
             plan.wp, plan.wt = packs[li].wp, packs[li].wt
@@ -388,7 +388,7 @@ class GeneratorFunction(torch.autograd.Function):
         if g_out is None:
             return (None,) * (3 + 4 * G_N)
         stages, prelu, refs = ctx.stages, ctx.prelu, ctx.param_refs
-        B, H, W = ctx.geom
+        B, _H, _W = ctx.geom
         dev, dt = g_out.device, stages[0].r.dtype
         dc = L.dtype_code(dt)
         g_out = g_out.contiguous().float()
@@ -587,7 +587,7 @@ class DiscriminatorFunction(torch.autograd.Function):
                         cur.record_stream(lane)
                 cin_real = ca + cb
                 for j, (_cin, cout, stride, _sn) in enumerate(layer_cfg):
-                    wgt, bias = params[2 * (sc * nl + j)], params[2 * (sc * nl + j) + 1]
+                    bias = params[2 * (sc * nl + j) + 1]
                     act = L.ACT_LRELU if j != nl - 1 else L.ACT_NONE
                     plan = ConvPlan(B, cur.shape[1], cur.shape[2], cur.shape[3], cin_real, cout, 4, stride, 2, act)
                     plan.wp, plan.wt, plan.w1x1 = packs[(sc, j)].wp, packs[(sc, j)].wt, packs[(sc, j)].w1x1
